@@ -1,0 +1,981 @@
+// Epoch engine: one handle per rank (= per GPU).  Mirrors gcn / dist_gcn<true,...>
+// (src/gcn.hpp:937-1056), gcn_layer / dist_gcn_layer (:411-637), sparse_linear / dist_sparse_linear
+// (:13-86), dist_row_linear (:191-296), the loss (:872-935) and the staged SpMM with its double
+// buffered exchange (src/cuda_utils.hpp:57-92, src/dist_matrix.hpp:458-467).
+//
+// What is different from the reference, by design:
+//   * device-resident buffers (one arena per rank) instead of cudaMallocManaged;
+//   * activation / activation-gradient / bias are epilogues of the kernel that produces the tensor
+//     (SpMM or GEMM), so every activation matrix makes one HBM round trip;
+//   * the exchange of the feature blocks has two back-ends: "nccl" = the reference's root-rotating
+//     ncclBroadcast schedule, and "p2p" = every rank pulls block (rank+s)%P at stage s straight out
+//     of the owner's arena over NVLink (copy engine, peer-mapped memory), so each stage is a
+//     permutation and every link is busy in every stage; stage 0 is the local block and needs no
+//     transfer at all.  Cross-rank ordering uses a flag barrier in peer-mapped memory;
+//   * weight gradients of all layers are reduced in one step (one ncclAllReduce, or in p2p mode a
+//     kernel that sums the peers' packed gradients in rank order) and Adam is one launch;
+//   * the whole epoch is captured into one CUDA graph (use_graph), removing ~100 launches and all
+//     the event bookkeeping of src/cuda_utils.hpp:61-91 from the host path.
+#include <dlfcn.h>
+#include <nccl.h>
+#include <unistd.h>
+
+#include <cmath>
+#include <string>
+#include <vector>
+
+#include "common.hpp"
+
+using namespace mggcn;
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------
+// NCCL is bound at run time (dlopen), so the library loads without it for P = 1 and shares the
+// copy torch already mapped when the host program is Python.
+// ---------------------------------------------------------------------------------------------
+struct nccl_api {
+    void *h = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+nccl_api g_nccl;
+
+int nccl_load() {
+    if (g_nccl.h) return MGGCN_OK;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    void *h = nullptr;
+    for (const char *n : names) {
+        h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (h) break;
+    }
+    if (!h) return fail(MGGCN_E_NCCL, "cannot load libnccl: %s", dlerror());
+#define BIND(field, sym)                                                        \
+    g_nccl.field = reinterpret_cast<decltype(g_nccl.field)>(dlsym(h, sym));     \
+    if (!g_nccl.field) return fail(MGGCN_E_NCCL, "libnccl lacks %s", sym)
+    BIND(GetUniqueId, "ncclGetUniqueId");
+    BIND(CommInitRank, "ncclCommInitRank");
+    BIND(CommDestroy, "ncclCommDestroy");
+    BIND(Broadcast, "ncclBroadcast");
+    BIND(AllReduce, "ncclAllReduce");
+    BIND(GroupStart, "ncclGroupStart");
+    BIND(GroupEnd, "ncclGroupEnd");
+    BIND(GetErrorString, "ncclGetErrorString");
+#undef BIND
+    g_nccl.h = h;
+    return MGGCN_OK;
+}
+
+#define NCCL_TRY(expr)                                                                          \
+    do {                                                                                        \
+        ncclResult_t r__ = (expr);                                                              \
+        if (r__ != ncclSuccess)                                                                 \
+            return fail(MGGCN_E_NCCL, "%s: %s", #expr, g_nccl.GetErrorString(r__));             \
+    } while (0)
+#define TRY(expr)                  \
+    do {                           \
+        int rc__ = (expr);         \
+        if (rc__) return rc__;     \
+    } while (0)
+
+inline int64_t up4(int64_t x) { return (x + 3) / 4 * 4; }
+inline size_t up256(size_t x) { return (x + 255) / 256 * 256; }
+
+// ---------------------------------------------------------------------------------------------
+// device helpers of the p2p back-end
+// ---------------------------------------------------------------------------------------------
+constexpr int kMaxRanks = 16;
+constexpr int kBarrierSlots = 128;
+struct peer_table {
+    uint32_t *flags[kMaxRanks];  // peer r's flag page (kBarrierSlots x kMaxRanks uint32)
+};
+
+// Flag barrier over peer-mapped memory.  Slot k has its own monotonically increasing ticket, kept
+// on the device so that a captured graph can be replayed.  Every rank runs the same sequence of
+// barriers, so the tickets agree.  A timeout (about 10 s of SM clock) raises *err instead of hanging.
+__global__ void xbarrier_kernel(peer_table pt, uint32_t *tickets, int slot, int rank, int P, int *err) {
+    __shared__ uint32_t ticket;
+    if (threadIdx.x == 0) ticket = ++tickets[slot];
+    __syncthreads();
+    const int t = threadIdx.x;
+    if (t < P) {
+        __threadfence_system();
+        volatile uint32_t *dst = pt.flags[t] + slot * kMaxRanks + rank;
+        *dst = ticket;
+        __threadfence_system();
+        volatile uint32_t *src = pt.flags[rank] + slot * kMaxRanks + t;
+        const long long t0 = clock64();
+        while ((int32_t)(*src - ticket) < 0) {
+            if (clock64() - t0 > 20000000000ll) {
+                *err = 1;
+                break;
+            }
+            __nanosleep(200);
+        }
+        __threadfence_system();
+    }
+}
+
+struct grad_peers {
+    const float *g[kMaxRanks];
+};
+// sum of the peers' packed gradients in rank order (identical on every rank)
+__global__ void grad_reduce_kernel(grad_peers gp, int P, size_t n, float *out) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int r = 0; r < P; ++r) s += gp.g[r][i];
+        out[i] = s;
+    }
+}
+
+// step counter and bias corrections live on the device so the Adam launch can sit in a graph
+// bc1 = (float)(1 - pow(beta1, t)), src/gcn.hpp:256-257
+__global__ void adam_prep_kernel(float *state, float beta1, float beta2) {
+    const float t = state[0] + 1.f;
+    state[0] = t;
+    state[1] = (float)(1.0 - pow((double)beta1, (double)t));
+    state[2] = (float)(1.0 - pow((double)beta2, (double)t));
+}
+__global__ void adam_dev_kernel(size_t n, float *p, float *g, float *m, float *v, const float *state, float lr,
+                                float beta1, float beta2, float wd, float eps, size_t n_decay) {
+    const float bc1 = state[1], bc2 = state[2];
+    const float step_size = lr / bc1;
+    const float a1 = 1.f - beta1, a2 = 1.f - beta2;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        float gi = g[i];
+        if (i < n_decay) {
+            gi = fmaf(wd, p[i], gi);
+            g[i] = gi;
+        }
+        const float mi = a1 * gi + beta1 * m[i];
+        const float vi = a2 * gi * gi + beta2 * v[i];
+        m[i] = mi;
+        v[i] = vi;
+        p[i] -= __fdividef(step_size * mi, sqrtf(__fdividef(vi, bc2)) + eps);
+    }
+}
+
+struct adj_block {
+    uint32_t *rowptr = nullptr, *colidx = nullptr;
+    float *vals = nullptr;
+    int64_t rows = 0, cols = 0, nnz = 0;
+    mggcn_spmm_plan_t *plan = nullptr;
+};
+
+struct layer_t {
+    int64_t in = 0, out = 0;
+    bool activation = false, gemm_first = false;
+    float *W = nullptr, *b = nullptr, *GW = nullptr, *Gb = nullptr;  // views into the packed vectors
+    float *Z = nullptr;   // layer output, n x up4(out)
+    float *AH = nullptr;  // exact_grads && !gemm_first: saved A*H, n x up4(in)
+};
+
+struct named_timer {
+    std::string name;
+    cudaEvent_t beg, end;
+};
+
+}  // namespace
+
+struct mggcn_engine {
+    int P = 1, rank = 0, device = 0, L = 0;
+    bool overlap = true, exact = false, use_graph = false, p2p = false, timers_on = false;
+    float slope = 0.01f;
+    int64_t N = 0, n = 0;  // global / local rows
+    std::vector<uint32_t> cuts;
+    std::vector<int64_t> sizes;
+    std::vector<layer_t> layers;
+    cudaStream_t sc = nullptr, sm = nullptr, scopy = nullptr;
+    ncclComm_t comm = nullptr;
+
+    adj_block adj[2][kMaxRanks];
+    bool adj_set[2] = {false, false};
+
+    // arena
+    char *arena = nullptr;
+    size_t arena_bytes = 0;
+    uint32_t *flags = nullptr;      // kBarrierSlots x kMaxRanks (first page of the arena)
+    float *X = nullptr;
+    int32_t *Y = nullptr;
+    int64_t ldX = 0;
+    float *HW = nullptr, *G[2] = {nullptr, nullptr}, *stage[2] = {nullptr, nullptr};
+    int64_t maxw = 0, max_block_rows = 0;
+    float *params = nullptr, *grads = nullptr, *gsum = nullptr, *adam_m = nullptr, *adam_v = nullptr;
+    size_t n_params = 0, n_weights = 0;
+    float *adam_state = nullptr;  // t, bc1, bc2
+    double *loss_out = nullptr;   // sum |log p_y|, #correct
+    void *ws_gemm = nullptr, *ws_colsum = nullptr, *ws_loss = nullptr, *ws_spmm = nullptr;
+    size_t ws_gemm_bytes = 0, ws_colsum_bytes = 0, ws_loss_bytes = 0, ws_spmm_bytes = 0;
+    uint32_t *tickets = nullptr;
+    int *dev_err = nullptr;
+
+    // p2p
+    char *peer_arena[kMaxRanks] = {nullptr};
+    bool peer_opened[kMaxRanks] = {false};
+    bool connected = false;
+    int barrier_next = 0;
+
+    // events (created once)
+    cudaEvent_t ev_ready = nullptr, ev_done = nullptr, ev_join = nullptr;
+    std::vector<cudaEvent_t> ev_xfer, ev_spmm;
+
+    // graph
+    cudaGraphExec_t graph_exec = nullptr;
+    float g_lr = 0, g_b1 = 0, g_b2 = 0, g_wd = 0, g_eps = 0;
+    int64_t launches_per_epoch = 0;
+    bool forward_done = false;
+
+    std::vector<named_timer> timers;
+    size_t timer_cursor = 0;
+};
+
+namespace {
+
+typedef mggcn_engine eng;
+
+int set_dev(const eng *e) {
+    MGGCN_CUDA_TRY(cudaSetDevice(e->device));
+    return MGGCN_OK;
+}
+
+template <typename T>
+T *carve(char *&cur, size_t count) {
+    T *p = reinterpret_cast<T *>(cur);
+    cur += up256(count * sizeof(T));
+    return p;
+}
+
+// timers: in eager mode every named region is bracketed by two events created on first use;
+// regions may nest and may sit on different streams, so begin hands out a slot and end takes it
+int timer_begin(eng *e, const std::string &name, cudaStream_t st, int *slot) {
+    *slot = -1;
+    if (!e->timers_on) return MGGCN_OK;
+    if (e->timer_cursor == e->timers.size()) {
+        named_timer t;
+        t.name = name;
+        MGGCN_CUDA_TRY(cudaEventCreate(&t.beg));
+        MGGCN_CUDA_TRY(cudaEventCreate(&t.end));
+        e->timers.push_back(t);
+    }
+    *slot = (int)e->timer_cursor++;
+    MGGCN_CUDA_TRY(cudaEventRecord(e->timers[*slot].beg, st));
+    return MGGCN_OK;
+}
+int timer_end(eng *e, cudaStream_t st, int slot) {
+    if (slot < 0) return MGGCN_OK;
+    MGGCN_CUDA_TRY(cudaEventRecord(e->timers[slot].end, st));
+    return MGGCN_OK;
+}
+
+int xbarrier(eng *e, cudaStream_t st) {
+    const int slot = e->barrier_next++;
+    if (slot >= kBarrierSlots) return fail(MGGCN_E_STATE, "too many barriers in one epoch");
+    peer_table pt{};
+    for (int r = 0; r < e->P; ++r) pt.flags[r] = reinterpret_cast<uint32_t *>(e->peer_arena[r]);
+    xbarrier_kernel<<<1, 32, 0, st>>>(pt, e->tickets, slot, e->rank, e->P, e->dev_err);
+    MGGCN_LAUNCH_CHECK();
+    return MGGCN_OK;
+}
+
+// C = A_which[rank][:] * B  (+ epilogue), B and C are this rank's row blocks (n x ld).
+// P stages with a double-buffered exchange; src/cuda_utils.hpp:57-92.
+int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggcn_epilogue *epi,
+              const std::string &tname) {
+    const int64_t ld = up4(F);
+    const int P = e->P;
+    if (P == 1) {
+        const adj_block &a = e->adj[which][0];
+        int ts;
+        TRY(timer_begin(e, tname + "matmul-spmm", e->sc, &ts));
+        TRY(mggcn_spmm_csr_f32_i32(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, B, ld, C, ld, (int)F, 1.f, 0.f,
+                                   epi, a.plan, e->ws_spmm));
+        TRY(timer_end(e, e->sc, ts));
+        return MGGCN_OK;
+    }
+    const size_t off = (size_t)(reinterpret_cast<const char *>(B) - e->arena);
+    MGGCN_CUDA_TRY(cudaEventRecord(e->ev_ready, e->sc));
+    if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sm, e->ev_ready, 0));
+    if (e->p2p) TRY(xbarrier(e, e->sm));  // every rank's B is complete
+    int t_all, t_x, t_s;
+    TRY(timer_begin(e, tname + "matmul-spmm", e->sc, &t_all));
+    for (int s = 0; s < P; ++s) {
+        const int blk = e->p2p ? (e->rank + s) % P : s;
+        const adj_block &a = e->adj[which][blk];
+        const float *src = B;
+        if (blk != e->rank || !e->p2p) {
+            // WAR: staging buffer s%2 was last read by the SpMM of stage s-2
+            if (s >= 2 && e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sm, e->ev_spmm[s - 2], 0));
+            const size_t count = (size_t)a.cols * (size_t)ld;
+            TRY(timer_begin(e, tname + std::to_string(s) + "_matmul-bcast", e->sm, &t_x));
+            if (e->p2p) {
+                MGGCN_CUDA_TRY(cudaMemcpyAsync(e->stage[s & 1], e->peer_arena[blk] + off, count * sizeof(float),
+                                               cudaMemcpyDeviceToDevice, e->sm));
+                src = e->stage[s & 1];
+            } else if (blk == e->rank) {
+                NCCL_TRY(g_nccl.Broadcast(B, const_cast<float *>(B), count, ncclFloat, blk, e->comm, e->sm));
+            } else {
+                NCCL_TRY(g_nccl.Broadcast(e->stage[s & 1], e->stage[s & 1], count, ncclFloat, blk, e->comm, e->sm));
+                src = e->stage[s & 1];
+            }
+            TRY(timer_end(e, e->sm, t_x));
+            if (e->sm != e->sc) {
+                MGGCN_CUDA_TRY(cudaEventRecord(e->ev_xfer[s], e->sm));
+                MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_xfer[s], 0));
+            }
+        }
+        const bool last = s == P - 1;
+        TRY(timer_begin(e, tname + std::to_string(s) + "_matmul-spmm-stage", e->sc, &t_s));
+        TRY(mggcn_spmm_csr_f32_i32(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, src, ld, C, ld, (int)F, 1.f,
+                                   s == 0 ? 0.f : 1.f, last ? epi : nullptr, a.plan, e->ws_spmm));
+        TRY(timer_end(e, e->sc, t_s));
+        if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaEventRecord(e->ev_spmm[s], e->sc));
+    }
+    TRY(timer_end(e, e->sc, t_all));
+    if (e->p2p) {
+        // nobody may overwrite B before every peer has pulled it
+        TRY(xbarrier(e, e->sm));
+        if (e->sm != e->sc) {
+            MGGCN_CUDA_TRY(cudaEventRecord(e->ev_done, e->sm));
+            MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_done, 0));
+        }
+    }
+    return MGGCN_OK;
+}
+
+int gemm(eng *e, int ta, int tb, int64_t M, int64_t N, int64_t K, const float *A, int64_t lda, const float *B,
+         int64_t ldb, float *C, int64_t ldc, const mggcn_epilogue *epi) {
+    return mggcn_gemm_f32(e->sc, ta, tb, M, N, K, 1.f, A, lda, B, ldb, 0.f, C, ldc, epi, e->ws_gemm, e->ws_gemm_bytes);
+}
+
+int forward(eng *e) {
+    int tg;
+    const float *H = e->X;
+    int64_t ldH = e->ldX;
+    for (int l = 0; l < e->L; ++l) {
+        layer_t &y = e->layers[l];
+        const std::string nm = std::to_string(l) + "_0_";
+        mggcn_epilogue act{};
+        act.kind = y.activation ? MGGCN_EPI_LEAKY_RELU : MGGCN_EPI_NONE;
+        act.slope = e->slope;
+        if (y.gemm_first) {
+            // HW = H W + b (bias in the GEMM epilogue); Z = act(A HW)
+            mggcn_epilogue bias{};
+            bias.bias = y.b;
+            TRY(timer_begin(e, nm + "matmul-gemm", e->sc, &tg));
+            TRY(gemm(e, 0, 0, e->n, y.out, y.in, H, ldH, y.W, y.out, e->HW, up4(y.out), &bias));
+            TRY(timer_end(e, e->sc, tg));
+            TRY(dist_spmm(e, 0, e->HW, y.Z, y.out, y.activation ? &act : nullptr, nm));
+        } else {
+            // AH = A H; Z = act(AH W + b)
+            float *AH = y.AH ? y.AH : e->HW;
+            TRY(dist_spmm(e, 0, H, AH, y.in, nullptr, nm));
+            act.bias = y.b;
+            TRY(timer_begin(e, nm + "matmul-gemm", e->sc, &tg));
+            TRY(gemm(e, 0, 0, e->n, y.out, y.in, AH, up4(y.in), y.W, y.out, y.Z, up4(y.out), &act));
+            TRY(timer_end(e, e->sc, tg));
+        }
+        H = y.Z;
+        ldH = up4(y.out);
+    }
+    layer_t &last = e->layers[e->L - 1];
+    TRY(timer_begin(e, std::to_string(e->L) + "_loss-layer", e->sc, &tg));
+    TRY(mggcn_softmax_xent_f32(e->sc, last.Z, up4(last.out), e->n, (int)last.out, e->Y, 1.f / (float)e->N,
+                               e->loss_out, e->ws_loss, e->ws_loss_bytes));
+    TRY(timer_end(e, e->sc, tg));
+    return MGGCN_OK;
+}
+
+int backward(eng *e) {
+    int tg;
+    const float *T = e->layers[e->L - 1].Z;  // (softmax - onehot)/N, written in place by the loss
+    for (int l = e->L - 1; l >= 0; --l) {
+        layer_t &y = e->layers[l];
+        const bool first = l == 0;
+        const std::string nm = std::to_string(l) + "_1_";
+        const float *Hin = first ? e->X : e->layers[l - 1].Z;
+        const int64_t ldHin = first ? e->ldX : up4(e->layers[l - 1].out);
+        float *Tprev = first ? nullptr : e->G[l & 1];
+        mggcn_epilogue dact{};  // gradient of layer l-1's LeakyReLU, fused into the producer of T_{l-1}
+        if (!first) {
+            dact.kind = MGGCN_EPI_LEAKY_RELU_BWD;
+            dact.slope = e->slope;
+            dact.aux = e->layers[l - 1].Z;
+            dact.ld_aux = up4(e->layers[l - 1].out);
+        }
+        const int64_t ldo = up4(y.out), ldi = up4(y.in);
+        if (y.gemm_first) {
+            const float *GHW = T;
+            if (!first || e->exact) {  // the reference skips this SpMM for layer 0
+                TRY(dist_spmm(e, 1, T, e->HW, y.out, nullptr, nm));
+                GHW = e->HW;
+            }
+            TRY(timer_begin(e, nm + "matmul-gemm", e->sc, &tg));
+            TRY(mggcn_colsum_f32(e->sc, e->n, y.out, GHW, ldo, y.Gb, e->ws_colsum, e->ws_colsum_bytes));
+            TRY(gemm(e, 1, 0, y.in, y.out, e->n, Hin, ldHin, GHW, ldo, y.GW, y.out, nullptr));
+            if (!first) TRY(gemm(e, 0, 1, e->n, y.in, y.out, GHW, ldo, y.W, y.out, Tprev, ldi, &dact));
+            TRY(timer_end(e, e->sc, tg));
+        } else {
+            // the reference uses the raw layer input H as the GEMM input here
+            const float *Xin = e->exact ? y.AH : Hin;
+            const int64_t ldXin = e->exact ? ldi : ldHin;
+            TRY(timer_begin(e, nm + "matmul-gemm", e->sc, &tg));
+            TRY(mggcn_colsum_f32(e->sc, e->n, y.out, T, ldo, y.Gb, e->ws_colsum, e->ws_colsum_bytes));
+            TRY(gemm(e, 1, 0, y.in, y.out, e->n, Xin, ldXin, T, ldo, y.GW, y.out, nullptr));
+            if (!first) TRY(gemm(e, 0, 1, e->n, y.in, y.out, T, ldo, y.W, y.out, e->HW, ldi, nullptr));
+            TRY(timer_end(e, e->sc, tg));
+            if (!first) TRY(dist_spmm(e, 1, e->HW, Tprev, y.in, &dact, nm));
+        }
+        T = Tprev;
+    }
+    // weight-gradient reduction over ranks (reference: one ncclAllReduce per tensor,
+    // src/dist_matrix.hpp:587-592 via src/gcn.hpp:238-240)
+    if (e->P > 1) {
+        TRY(timer_begin(e, "allreduce", e->sc, &tg));
+        if (e->p2p) {
+            MGGCN_CUDA_TRY(cudaEventRecord(e->ev_ready, e->sc));
+            if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sm, e->ev_ready, 0));
+            TRY(xbarrier(e, e->sm));
+            if (e->sm != e->sc) {
+                MGGCN_CUDA_TRY(cudaEventRecord(e->ev_done, e->sm));
+                MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_done, 0));
+            }
+            grad_peers gp{};
+            const size_t off = (size_t)(reinterpret_cast<char *>(e->grads) - e->arena);
+            for (int r = 0; r < e->P; ++r) gp.g[r] = reinterpret_cast<const float *>(e->peer_arena[r] + off);
+            grad_reduce_kernel<<<(unsigned)std::max<size_t>(1, std::min<size_t>((e->n_params + 255) / 256, 296)), 256, 0,
+                                 e->sc>>>(gp, e->P, e->n_params, e->gsum);
+            MGGCN_LAUNCH_CHECK();
+        } else {
+            NCCL_TRY(g_nccl.AllReduce(e->grads, e->gsum, e->n_params, ncclFloat, ncclSum, e->comm, e->sc));
+        }
+        TRY(timer_end(e, e->sc, tg));
+    }
+    return MGGCN_OK;
+}
+
+int adam(eng *e, float lr, float b1, float b2, float wd, float eps) {
+    int tg;
+    TRY(timer_begin(e, "adam-update", e->sc, &tg));
+    adam_prep_kernel<<<1, 1, 0, e->sc>>>(e->adam_state, b1, b2);
+    MGGCN_LAUNCH_CHECK();
+    const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((e->n_params + 255) / 256, 148 * 4));
+    adam_dev_kernel<<<grid, 256, 0, e->sc>>>(e->n_params, e->params, e->gsum, e->adam_m, e->adam_v, e->adam_state, lr,
+                                             b1, b2, wd, eps, e->n_weights);
+    MGGCN_LAUNCH_CHECK();
+    TRY(timer_end(e, e->sc, tg));
+    return MGGCN_OK;
+}
+
+int check_ready(eng *e) {
+    if (!e->adj_set[0] || !e->adj_set[1]) return fail(MGGCN_E_STATE, "adjacency not set");
+    if (e->P > 1 && e->p2p && !e->connected) return fail(MGGCN_E_STATE, "p2p engine not connected to its peers");
+    return MGGCN_OK;
+}
+
+void begin_pass(eng *e) {
+    e->barrier_next = 0;
+    e->timer_cursor = 0;
+}
+
+int epoch_body(eng *e, float lr, float b1, float b2, float wd, float eps) {
+    begin_pass(e);
+    TRY(forward(e));
+    TRY(backward(e));
+    TRY(adam(e, lr, b1, b2, wd, eps));
+    return MGGCN_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mggcn_nccl_unique_id(void *id128) {
+    if (!id128) return fail(MGGCN_E_INVALID, "null id");
+    TRY(nccl_load());
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    NCCL_TRY(g_nccl.GetUniqueId(static_cast<ncclUniqueId *>(id128)));
+    return MGGCN_OK;
+}
+
+int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
+    if (!cfg || !out) return fail(MGGCN_E_INVALID, "null argument");
+    if (cfg->world < 1 || cfg->world > kMaxRanks || cfg->rank < 0 || cfg->rank >= cfg->world)
+        return fail(MGGCN_E_INVALID, "bad world/rank %d/%d", cfg->world, cfg->rank);
+    if (cfg->num_layers < 1 || !cfg->sizes || !cfg->p) return fail(MGGCN_E_INVALID, "bad layer description");
+    auto *e = new (std::nothrow) mggcn_engine;
+    if (!e) return fail(MGGCN_E_NOMEM, "out of memory");
+    e->P = cfg->world;
+    e->rank = cfg->rank;
+    e->device = cfg->device;
+    e->L = cfg->num_layers;
+    e->overlap = cfg->overlap != 0;
+    e->exact = cfg->exact_grads != 0;
+    e->use_graph = cfg->use_graph != 0;
+    e->p2p = cfg->comm_backend == MGGCN_COMM_P2P && cfg->world > 1;
+    e->timers_on = cfg->timers != 0 && !e->use_graph;
+    e->slope = cfg->lrelu_slope;
+    e->N = cfg->n_global;
+    e->cuts.assign(cfg->p, cfg->p + e->P + 1);
+    e->n = (int64_t)e->cuts[e->rank + 1] - (int64_t)e->cuts[e->rank];
+    e->sizes.assign(cfg->sizes, cfg->sizes + e->L + 1);
+    for (int64_t s : e->sizes)
+        if (s <= 0) { delete e; return fail(MGGCN_E_INVALID, "layer width must be positive"); }
+#define E_TRY(expr)                                  \
+    do {                                             \
+        int rc__ = (expr);                           \
+        if (rc__) { mggcn_engine_destroy(e); return rc__; } \
+    } while (0)
+#define E_CUDA(expr)                                                                                 \
+    do {                                                                                             \
+        cudaError_t ce__ = (expr);                                                                   \
+        if (ce__ != cudaSuccess) {                                                                   \
+            mggcn_engine_destroy(e);                                                                 \
+            return fail((int)ce__, "%s: %s", #expr, cudaGetErrorString(ce__));                      \
+        }                                                                                            \
+    } while (0)
+    E_CUDA(cudaSetDevice(e->device));
+    int lo = 0, hi = 0;
+    E_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    // compute = low priority, exchange = high priority (src/matrix.hpp:53-60,82)
+    E_CUDA(cudaStreamCreateWithPriority(&e->sc, cudaStreamNonBlocking, lo));
+    if (e->overlap && e->P > 1) E_CUDA(cudaStreamCreateWithPriority(&e->sm, cudaStreamNonBlocking, hi));
+    else e->sm = e->sc;
+    E_CUDA(cudaStreamCreateWithFlags(&e->scopy, cudaStreamNonBlocking));
+    E_CUDA(cudaEventCreateWithFlags(&e->ev_ready, cudaEventDisableTiming));
+    E_CUDA(cudaEventCreateWithFlags(&e->ev_done, cudaEventDisableTiming));
+    E_CUDA(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+    e->ev_xfer.resize(e->P);
+    e->ev_spmm.resize(e->P);
+    for (int i = 0; i < e->P; ++i) {
+        E_CUDA(cudaEventCreateWithFlags(&e->ev_xfer[i], cudaEventDisableTiming));
+        E_CUDA(cudaEventCreateWithFlags(&e->ev_spmm[i], cudaEventDisableTiming));
+    }
+
+    // ---- layers and sizes
+    e->layers.resize(e->L);
+    e->n_weights = 0;
+    size_t n_bias = 0;
+    e->maxw = up4(e->sizes[0]);
+    for (int l = 0; l < e->L; ++l) {
+        layer_t &y = e->layers[l];
+        y.in = e->sizes[l];
+        y.out = e->sizes[l + 1];
+        y.activation = l + 1 < e->L;      // src/gcn.hpp:954,1023
+        y.gemm_first = y.out <= y.in;     // src/gcn.hpp:439,558
+        e->n_weights += (size_t)(y.in * y.out);
+        n_bias += (size_t)y.out;
+        e->maxw = std::max(e->maxw, up4(y.out));
+    }
+    e->n_params = e->n_weights + n_bias;
+    for (int i = 0; i < e->P; ++i)
+        e->max_block_rows = std::max<int64_t>(e->max_block_rows, (int64_t)e->cuts[i + 1] - (int64_t)e->cuts[i]);
+    e->ldX = up4(e->sizes[0]);
+
+    for (int l = 0; l < e->L; ++l) {
+        const layer_t &y = e->layers[l];
+        e->ws_gemm_bytes = std::max(e->ws_gemm_bytes, mggcn_gemm_workspace_bytes(1, 0, y.in, y.out, e->n));
+        e->ws_colsum_bytes = std::max(e->ws_colsum_bytes, mggcn_colsum_workspace_bytes(e->n, y.out));
+    }
+    e->ws_loss_bytes = mggcn_softmax_xent_workspace_bytes(e->n);
+
+    // ---- arena
+    const size_t n = (size_t)e->n;
+    size_t total = 0;
+    auto need = [&](size_t bytes) { total += up256(bytes); };
+    need(sizeof(uint32_t) * kBarrierSlots * kMaxRanks);           // flags
+    need(n * (size_t)e->ldX * 4);                                  // X
+    need(n * 4);                                                   // Y
+    need(n * (size_t)e->maxw * 4);                                 // HW
+    need(n * (size_t)e->maxw * 4);                                 // G0
+    need(n * (size_t)e->maxw * 4);                                 // G1
+    if (e->P > 1) {
+        need((size_t)e->max_block_rows * (size_t)e->maxw * 4);
+        need((size_t)e->max_block_rows * (size_t)e->maxw * 4);
+    }
+    for (int l = 0; l < e->L; ++l) {
+        need(n * (size_t)up4(e->layers[l].out) * 4);
+        if (e->exact && !e->layers[l].gemm_first) need(n * (size_t)up4(e->layers[l].in) * 4);
+    }
+    for (int k = 0; k < 5; ++k) need(e->n_params * 4);  // params grads gsum m v
+    need(16);                                           // adam_state
+    need(16);                                           // loss_out
+    need(e->ws_gemm_bytes);
+    need(e->ws_colsum_bytes);
+    need(e->ws_loss_bytes);
+    need(sizeof(uint32_t) * kBarrierSlots);
+    need(16);
+    e->arena_bytes = total + 4096;
+    E_CUDA(cudaMalloc(&e->arena, e->arena_bytes));
+    E_CUDA(cudaMemset(e->arena, 0, e->arena_bytes));
+    char *cur = e->arena;
+    e->flags = carve<uint32_t>(cur, kBarrierSlots * kMaxRanks);
+    e->X = carve<float>(cur, n * (size_t)e->ldX);
+    e->Y = carve<int32_t>(cur, n);
+    e->HW = carve<float>(cur, n * (size_t)e->maxw);
+    e->G[0] = carve<float>(cur, n * (size_t)e->maxw);
+    e->G[1] = carve<float>(cur, n * (size_t)e->maxw);
+    if (e->P > 1) {
+        e->stage[0] = carve<float>(cur, (size_t)e->max_block_rows * (size_t)e->maxw);
+        e->stage[1] = carve<float>(cur, (size_t)e->max_block_rows * (size_t)e->maxw);
+    }
+    for (int l = 0; l < e->L; ++l) {
+        e->layers[l].Z = carve<float>(cur, n * (size_t)up4(e->layers[l].out));
+        if (e->exact && !e->layers[l].gemm_first) e->layers[l].AH = carve<float>(cur, n * (size_t)up4(e->layers[l].in));
+    }
+    e->params = carve<float>(cur, e->n_params);
+    e->grads = carve<float>(cur, e->n_params);
+    e->gsum = e->P > 1 ? carve<float>(cur, e->n_params) : e->grads;
+    if (e->P == 1) carve<float>(cur, e->n_params);
+    e->adam_m = carve<float>(cur, e->n_params);
+    e->adam_v = carve<float>(cur, e->n_params);
+    e->adam_state = carve<float>(cur, 4);
+    e->loss_out = carve<double>(cur, 2);
+    e->ws_gemm = e->ws_gemm_bytes ? carve<char>(cur, e->ws_gemm_bytes) : nullptr;
+    e->ws_colsum = carve<char>(cur, e->ws_colsum_bytes);
+    e->ws_loss = carve<char>(cur, e->ws_loss_bytes);
+    e->tickets = carve<uint32_t>(cur, kBarrierSlots);
+    e->dev_err = carve<int>(cur, 4);
+    e->peer_arena[e->rank] = e->arena;
+
+    // ---- parameters: packed [W_0 .. W_{L-1} | b_0 .. b_{L-1}], reference init (src/gcn.hpp:211-214)
+    {
+        std::vector<float> host(e->n_params);
+        size_t wo = 0, bo = e->n_weights;
+        for (int l = 0; l < e->L; ++l) {
+            layer_t &y = e->layers[l];
+            y.W = e->params + wo;
+            y.GW = e->grads + wo;
+            y.b = e->params + bo;
+            y.Gb = e->grads + bo;
+            E_TRY(mggcn_init_weights(y.in, y.out, (float)std::sqrt(2.0 / (1.0 + 0.01 * 0.01)), host.data() + wo));
+            E_TRY(mggcn_init_weights(1, y.out, std::sqrt(1.f / 3.f), host.data() + bo));
+            wo += (size_t)(y.in * y.out);
+            bo += (size_t)y.out;
+        }
+        E_CUDA(cudaMemcpy(e->params, host.data(), e->n_params * 4, cudaMemcpyHostToDevice));
+    }
+
+    if (e->P > 1 && !e->p2p) {
+        if (!cfg->nccl_id) { mggcn_engine_destroy(e); return fail(MGGCN_E_INVALID, "nccl_id is required when world > 1"); }
+        E_TRY(nccl_load());
+        ncclUniqueId id;
+        memcpy(&id, cfg->nccl_id, sizeof id);
+        ncclResult_t r = g_nccl.CommInitRank(&e->comm, e->P, id, e->rank);
+        if (r != ncclSuccess) {
+            mggcn_engine_destroy(e);
+            return fail(MGGCN_E_NCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString(r));
+        }
+    }
+#undef E_TRY
+#undef E_CUDA
+    *out = e;
+    return MGGCN_OK;
+}
+
+int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *const *blk_rowptr,
+                               const uint32_t *const *blk_colidx, const float *const *blk_vals) {
+    if (!e || which < 0 || which > 1 || !blk_rowptr || !blk_colidx || !blk_vals) return fail(MGGCN_E_INVALID, "bad argument");
+    TRY(set_dev(e));
+    size_t ws = e->ws_spmm_bytes;
+    for (int j = 0; j < e->P; ++j) {
+        adj_block &a = e->adj[which][j];
+        if (a.plan) { mggcn_spmm_plan_destroy(a.plan); a.plan = nullptr; }
+        if (a.rowptr) { cudaFree(a.rowptr); a.rowptr = nullptr; }
+        if (a.colidx) { cudaFree(a.colidx); a.colidx = nullptr; }
+        if (a.vals) { cudaFree(a.vals); a.vals = nullptr; }
+        a.rows = e->n;
+        a.cols = (int64_t)e->cuts[j + 1] - (int64_t)e->cuts[j];
+        const uint64_t *rp = blk_rowptr[j];
+        a.nnz = (int64_t)rp[a.rows];
+        if ((uint64_t)a.nnz > 0xFFFFFFFFull) return fail(MGGCN_E_UNSUPPORTED, "block nnz exceeds 32 bits");
+        // after the P x P split every block's local row pointers fit 32 bits
+        std::vector<uint32_t> rp32((size_t)a.rows + 1);
+        for (int64_t r = 0; r <= a.rows; ++r) rp32[(size_t)r] = (uint32_t)rp[r];
+        MGGCN_CUDA_TRY(cudaMalloc(&a.rowptr, rp32.size() * 4));
+        MGGCN_CUDA_TRY(cudaMemcpy(a.rowptr, rp32.data(), rp32.size() * 4, cudaMemcpyHostToDevice));
+        MGGCN_CUDA_TRY(cudaMalloc(&a.colidx, std::max<size_t>((size_t)a.nnz, 1) * 4));
+        MGGCN_CUDA_TRY(cudaMalloc(&a.vals, std::max<size_t>((size_t)a.nnz, 1) * 4));
+        MGGCN_CUDA_TRY(cudaMemcpy(a.colidx, blk_colidx[j], (size_t)a.nnz * 4, cudaMemcpyHostToDevice));
+        MGGCN_CUDA_TRY(cudaMemcpy(a.vals, blk_vals[j], (size_t)a.nnz * 4, cudaMemcpyHostToDevice));
+        TRY(mggcn_spmm_plan_create_i32(a.rows, rp32.data(), 0, &a.plan));
+        ws = std::max(ws, mggcn_spmm_plan_workspace_bytes(a.plan, (int)e->maxw));
+    }
+    if (ws > e->ws_spmm_bytes) {
+        if (e->ws_spmm) cudaFree(e->ws_spmm);
+        MGGCN_CUDA_TRY(cudaMalloc(&e->ws_spmm, ws));
+        e->ws_spmm_bytes = ws;
+    }
+    e->adj_set[which] = true;
+    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+    return MGGCN_OK;
+}
+
+int mggcn_engine_set_inputs(mggcn_engine_t *e, const float *X_host, const int32_t *Y_host, int async) {
+    if (!e) return fail(MGGCN_E_INVALID, "null engine");
+    TRY(set_dev(e));
+    // ordered after everything already queued on the compute stream (the previous epoch reads X)
+    cudaStream_t st = e->sc;
+    if (X_host)
+        MGGCN_CUDA_TRY(cudaMemcpy2DAsync(e->X, (size_t)e->ldX * 4, X_host, (size_t)e->sizes[0] * 4, (size_t)e->sizes[0] * 4,
+                                         (size_t)e->n, cudaMemcpyHostToDevice, st));
+    if (Y_host) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y, Y_host, (size_t)e->n * 4, cudaMemcpyHostToDevice, st));
+    if (!async) MGGCN_CUDA_TRY(cudaStreamSynchronize(st));
+    return MGGCN_OK;
+}
+
+int mggcn_engine_comm_handle(mggcn_engine_t *e, void *out, size_t cap, size_t *len) {
+    if (!e || !len) return fail(MGGCN_E_INVALID, "bad argument");
+    const size_t need = sizeof(int64_t) * 2 + sizeof(cudaIpcMemHandle_t);
+    *len = need;
+    if (!out) return MGGCN_OK;
+    if (cap < need) return fail(MGGCN_E_INVALID, "handle buffer too small");
+    TRY(set_dev(e));
+    char *o = static_cast<char *>(out);
+    const int64_t pid = (int64_t)getpid();
+    const int64_t ptr = (int64_t)reinterpret_cast<uintptr_t>(e->arena);
+    memcpy(o, &pid, 8);
+    memcpy(o + 8, &ptr, 8);
+    cudaIpcMemHandle_t h;
+    memset(&h, 0, sizeof h);
+    if (e->p2p) MGGCN_CUDA_TRY(cudaIpcGetMemHandle(&h, e->arena));
+    memcpy(o + 16, &h, sizeof h);
+    return MGGCN_OK;
+}
+
+int mggcn_engine_comm_connect(mggcn_engine_t *e, const void *handles, size_t len) {
+    if (!e || !handles) return fail(MGGCN_E_INVALID, "bad argument");
+    if (!e->p2p) return MGGCN_OK;
+    const size_t need = sizeof(int64_t) * 2 + sizeof(cudaIpcMemHandle_t);
+    if (len != need) return fail(MGGCN_E_INVALID, "handle length mismatch");
+    TRY(set_dev(e));
+    const char *hs = static_cast<const char *>(handles);
+    for (int r = 0; r < e->P; ++r) {
+        if (r == e->rank) continue;
+        int64_t pid, ptr;
+        memcpy(&pid, hs + (size_t)r * need, 8);
+        memcpy(&ptr, hs + (size_t)r * need + 8, 8);
+        if (pid == (int64_t)getpid()) {
+            // same process (the mg_gcn CLI drives all GPUs from one process): plain peer access
+            cudaPointerAttributes attr;
+            MGGCN_CUDA_TRY(cudaPointerGetAttributes(&attr, reinterpret_cast<void *>((uintptr_t)ptr)));
+            cudaError_t pe = cudaDeviceEnablePeerAccess(attr.device, 0);
+            if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled)
+                return fail((int)pe, "cudaDeviceEnablePeerAccess(%d): %s", attr.device, cudaGetErrorString(pe));
+            cudaGetLastError();
+            e->peer_arena[r] = reinterpret_cast<char *>((uintptr_t)ptr);
+        } else {
+            cudaIpcMemHandle_t h;
+            memcpy(&h, hs + (size_t)r * need + 16, sizeof h);
+            void *p = nullptr;
+            MGGCN_CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+            e->peer_arena[r] = static_cast<char *>(p);
+            e->peer_opened[r] = true;
+        }
+    }
+    e->connected = true;
+    return MGGCN_OK;
+}
+
+int mggcn_engine_train_forward(mggcn_engine_t *e) {
+    if (!e) return fail(MGGCN_E_INVALID, "null engine");
+    TRY(check_ready(e));
+    TRY(set_dev(e));
+    begin_pass(e);
+    TRY(forward(e));
+    e->forward_done = true;
+    return MGGCN_OK;
+}
+
+int mggcn_engine_backward(mggcn_engine_t *e) {
+    if (!e) return fail(MGGCN_E_INVALID, "null engine");
+    if (!e->forward_done) return fail(MGGCN_E_STATE, "backward before train_forward");
+    TRY(set_dev(e));
+    TRY(backward(e));
+    e->forward_done = false;
+    return MGGCN_OK;
+}
+
+int mggcn_engine_adam_update(mggcn_engine_t *e, float lr, float beta1, float beta2, float wd, float eps) {
+    if (!e) return fail(MGGCN_E_INVALID, "null engine");
+    TRY(set_dev(e));
+    return adam(e, lr, beta1, beta2, wd, eps);
+}
+
+int mggcn_engine_epoch(mggcn_engine_t *e, float lr, float beta1, float beta2, float wd, float eps) {
+    if (!e) return fail(MGGCN_E_INVALID, "null engine");
+    TRY(check_ready(e));
+    TRY(set_dev(e));
+    if (!e->use_graph) {
+        const uint64_t before = mggcn_launch_count();
+        TRY(epoch_body(e, lr, beta1, beta2, wd, eps));
+        e->launches_per_epoch = (int64_t)(mggcn_launch_count() - before);
+        return MGGCN_OK;
+    }
+    if (e->graph_exec && (lr != e->g_lr || beta1 != e->g_b1 || beta2 != e->g_b2 || wd != e->g_wd || eps != e->g_eps)) {
+        cudaGraphExecDestroy(e->graph_exec);
+        e->graph_exec = nullptr;
+    }
+    if (!e->graph_exec) {
+        cudaGraph_t graph = nullptr;
+        const uint64_t before = mggcn_launch_count();
+        MGGCN_CUDA_TRY(cudaStreamBeginCapture(e->sc, cudaStreamCaptureModeThreadLocal));
+        int rc = epoch_body(e, lr, beta1, beta2, wd, eps);
+        if (rc == MGGCN_OK && e->sm != e->sc) {
+            // join the exchange stream back into the origin stream before the capture ends
+            cudaError_t ce = cudaEventRecord(e->ev_join, e->sm);
+            if (ce == cudaSuccess) ce = cudaStreamWaitEvent(e->sc, e->ev_join, 0);
+            if (ce != cudaSuccess) rc = fail((int)ce, "graph join: %s", cudaGetErrorString(ce));
+        }
+        cudaError_t ce = cudaStreamEndCapture(e->sc, &graph);
+        if (rc) {
+            if (graph) cudaGraphDestroy(graph);
+            return rc;
+        }
+        if (ce != cudaSuccess) return fail((int)ce, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
+        e->launches_per_epoch = (int64_t)(mggcn_launch_count() - before);
+        ce = cudaGraphInstantiate(&e->graph_exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ce != cudaSuccess) return fail((int)ce, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
+        e->g_lr = lr; e->g_b1 = beta1; e->g_b2 = beta2; e->g_wd = wd; e->g_eps = eps;
+    } else {
+        count_launch((uint64_t)e->launches_per_epoch);
+    }
+    MGGCN_CUDA_TRY(cudaGraphLaunch(e->graph_exec, e->sc));
+    return MGGCN_OK;
+}
+
+int mggcn_engine_sync(mggcn_engine_t *e) {
+    if (!e) return fail(MGGCN_E_INVALID, "null engine");
+    TRY(set_dev(e));
+    MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
+    if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sm));
+    int err = 0;
+    MGGCN_CUDA_TRY(cudaMemcpy(&err, e->dev_err, sizeof err, cudaMemcpyDeviceToHost));
+    if (err) return fail(MGGCN_E_STATE, "peer barrier timed out (a rank is missing or died)");
+    return MGGCN_OK;
+}
+
+int mggcn_engine_loss(mggcn_engine_t *e, double *loss_sum, double *correct) {
+    if (!e) return fail(MGGCN_E_INVALID, "null engine");
+    TRY(set_dev(e));
+    double h[2] = {0, 0};
+    MGGCN_CUDA_TRY(cudaMemcpyAsync(h, e->loss_out, sizeof h, cudaMemcpyDeviceToHost, e->sc));
+    MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
+    if (loss_sum) *loss_sum = h[0];
+    if (correct) *correct = h[1];
+    return MGGCN_OK;
+}
+
+void *mggcn_engine_stream(mggcn_engine_t *e, int which) {
+    if (!e) return nullptr;
+    return which == 0 ? e->sc : which == 1 ? e->sm : e->scopy;
+}
+
+static int find_tensor(mggcn_engine_t *e, const char *name, float **ptr, int64_t *rows, int64_t *cols, int64_t *ld) {
+    if (!name || !name[0]) return fail(MGGCN_E_INVALID, "empty tensor name");
+    const bool g = name[0] == 'G';
+    const int l = atoi(name + (g ? 2 : 1));
+    if (l < 0 || l >= e->L) return fail(MGGCN_E_INVALID, "no layer %d", l);
+    layer_t &y = e->layers[l];
+    if (name[0] == 'W') { *ptr = y.W; *rows = y.in; *cols = y.out; *ld = y.out; }
+    else if (name[0] == 'b') { *ptr = y.b; *rows = 1; *cols = y.out; *ld = y.out; }
+    else if (g && name[1] == 'W') { *ptr = y.GW - e->grads + e->gsum; *rows = y.in; *cols = y.out; *ld = y.out; }
+    else if (g && name[1] == 'b') { *ptr = y.Gb - e->grads + e->gsum; *rows = 1; *cols = y.out; *ld = y.out; }
+    else if (name[0] == 'H') { *ptr = y.Z; *rows = e->n; *cols = y.out; *ld = up4(y.out); }
+    else return fail(MGGCN_E_INVALID, "unknown tensor %s", name);
+    return MGGCN_OK;
+}
+
+int mggcn_engine_get(mggcn_engine_t *e, const char *name, float *out, size_t cap, size_t *count) {
+    if (!e || !count) return fail(MGGCN_E_INVALID, "bad argument");
+    TRY(set_dev(e));
+    float *p; int64_t r, c, ld;
+    TRY(find_tensor(e, name, &p, &r, &c, &ld));
+    *count = (size_t)(r * c);
+    if (!out) return MGGCN_OK;
+    if (cap < *count) return fail(MGGCN_E_INVALID, "buffer too small for %s", name);
+    TRY(mggcn_engine_sync(e));
+    MGGCN_CUDA_TRY(cudaMemcpy2D(out, (size_t)c * 4, p, (size_t)ld * 4, (size_t)c * 4, (size_t)r, cudaMemcpyDeviceToHost));
+    return MGGCN_OK;
+}
+
+int mggcn_engine_set(mggcn_engine_t *e, const char *name, const float *in, size_t count) {
+    if (!e || !in) return fail(MGGCN_E_INVALID, "bad argument");
+    TRY(set_dev(e));
+    float *p; int64_t r, c, ld;
+    TRY(find_tensor(e, name, &p, &r, &c, &ld));
+    if (count != (size_t)(r * c)) return fail(MGGCN_E_INVALID, "%s has %lld elements", name, (long long)(r * c));
+    TRY(mggcn_engine_sync(e));
+    MGGCN_CUDA_TRY(cudaMemcpy2D(p, (size_t)ld * 4, in, (size_t)c * 4, (size_t)c * 4, (size_t)r, cudaMemcpyHostToDevice));
+    return MGGCN_OK;
+}
+
+int mggcn_engine_dump_timers(mggcn_engine_t *e, const char *prefix, char *buf, size_t cap, size_t *written) {
+    if (!e || !written) return fail(MGGCN_E_INVALID, "bad argument");
+    TRY(mggcn_engine_sync(e));
+    std::string s;
+    for (const named_timer &t : e->timers) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, t.beg, t.end) != cudaSuccess) { cudaGetLastError(); continue; }
+        s += (prefix ? prefix : "");
+        s += t.name + ":" + std::to_string(ms) + "\n";  // "<name>:<ms>\n", src/matrix.hpp:149-157
+    }
+    *written = s.size();
+    if (buf && cap) {
+        const size_t k = std::min(cap - 1, s.size());
+        memcpy(buf, s.data(), k);
+        buf[k] = 0;
+    }
+    return MGGCN_OK;
+}
+
+int64_t mggcn_engine_launches_per_epoch(mggcn_engine_t *e) { return e ? e->launches_per_epoch : 0; }
+
+void mggcn_engine_destroy(mggcn_engine_t *e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->sc) cudaStreamSynchronize(e->sc);
+    if (e->sm && e->sm != e->sc) cudaStreamSynchronize(e->sm);
+    if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
+    if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
+    for (int r = 0; r < e->P; ++r)
+        if (e->peer_opened[r]) cudaIpcCloseMemHandle(e->peer_arena[r]);
+    for (int w = 0; w < 2; ++w)
+        for (int j = 0; j < kMaxRanks; ++j) {
+            adj_block &a = e->adj[w][j];
+            if (a.plan) mggcn_spmm_plan_destroy(a.plan);
+            if (a.rowptr) cudaFree(a.rowptr);
+            if (a.colidx) cudaFree(a.colidx);
+            if (a.vals) cudaFree(a.vals);
+        }
+    if (e->ws_spmm) cudaFree(e->ws_spmm);
+    if (e->arena) cudaFree(e->arena);
+    for (named_timer &t : e->timers) { cudaEventDestroy(t.beg); cudaEventDestroy(t.end); }
+    for (cudaEvent_t ev : e->ev_xfer) if (ev) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : e->ev_spmm) if (ev) cudaEventDestroy(ev);
+    if (e->ev_ready) cudaEventDestroy(e->ev_ready);
+    if (e->ev_done) cudaEventDestroy(e->ev_done);
+    if (e->ev_join) cudaEventDestroy(e->ev_join);
+    if (e->sm && e->sm != e->sc) cudaStreamDestroy(e->sm);
+    if (e->sc) cudaStreamDestroy(e->sc);
+    if (e->scopy) cudaStreamDestroy(e->scopy);
+    cudaGetLastError();
+    delete e;
+}
+
+int mggcn_bcast_stage_f32(void *nccl_comm, mggcn_stream_t stream, const float *send, float *recv, size_t count,
+                          int root) {
+    if (!nccl_comm) return fail(MGGCN_E_INVALID, "null communicator");
+    TRY(nccl_load());
+    NCCL_TRY(g_nccl.Broadcast(send, recv, count, ncclFloat, root, static_cast<ncclComm_t>(nccl_comm),
+                              static_cast<cudaStream_t>(stream)));
+    return MGGCN_OK;
+}
+
+}  // extern "C"

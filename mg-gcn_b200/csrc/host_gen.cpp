@@ -1,0 +1,248 @@
+// Synthetic dataset generator: stands in for /root/reference/test/data/prep.py (which downloads
+// reddit / ogbn-* through dgl and ogb; no network here) and writes the same shapes:
+//   prep.py:101-126  N and F padded up to multiples of 8 with isolated, zero-feature, label-0
+//                    nodes; one self-loop per node (add_self_loop); unit weights;
+//   prep.py:87-94    optional seeded symmetric permutation ("test/data/permuted/<name>").
+// Edges are sampled with a counter-based hash, so the graph depends only on the arguments, never
+// on the thread count.
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <omp.h>
+#include <random>
+#include <vector>
+
+#include "common.hpp"
+
+using namespace mggcn;
+
+struct mggcn_gen {
+    int64_t n = 0;
+    std::vector<uint64_t> rowptr;
+    std::vector<uint32_t> colidx;
+};
+
+namespace {
+
+// new_id = perm[old_id]; identity when seed == 0 (prep.py: seed 0 means "not permuted")
+std::vector<uint32_t> make_perm(int64_t n, uint64_t seed) {
+    std::vector<uint32_t> perm((size_t)n);
+    for (int64_t i = 0; i < n; ++i) perm[i] = (uint32_t)i;
+    if (seed == 0) return perm;
+    for (int64_t i = n - 1; i > 0; --i) {  // Fisher-Yates driven by the counter hash
+        uint64_t j = hash2(seed ^ 0x5045524Dull, (uint64_t)i) % (uint64_t)(i + 1);
+        std::swap(perm[i], perm[j]);
+    }
+    return perm;
+}
+
+// Vose alias table over n weights
+struct alias_table {
+    std::vector<float> prob;
+    std::vector<uint32_t> alias;
+    void build(const std::vector<double> &w) {
+        const size_t n = w.size();
+        prob.assign(n, 0.f);
+        alias.assign(n, 0);
+        double total = 0;
+        for (double x : w) total += x;
+        std::vector<double> scaled(n);
+        std::vector<uint32_t> small, large;
+        small.reserve(n);
+        large.reserve(n);
+        for (size_t i = 0; i < n; ++i) {
+            scaled[i] = w[i] * (double)n / total;
+            (scaled[i] < 1.0 ? small : large).push_back((uint32_t)i);
+        }
+        while (!small.empty() && !large.empty()) {
+            uint32_t s = small.back(), l = large.back();
+            small.pop_back();
+            prob[s] = (float)scaled[s];
+            alias[s] = l;
+            scaled[l] = (scaled[l] + scaled[s]) - 1.0;
+            if (scaled[l] < 1.0) { large.pop_back(); small.push_back(l); }
+        }
+        for (uint32_t i : large) { prob[i] = 1.f; alias[i] = i; }
+        for (uint32_t i : small) { prob[i] = 1.f; alias[i] = i; }
+    }
+    inline uint32_t sample(uint64_t h) const {
+        const size_t n = prob.size();
+        uint64_t slot = (h >> 32) * (uint64_t)n >> 32;           // top 32 bits pick the slot
+        float u = (float)(h & 0xFFFFFFull) * (1.0f / 16777216.0f);  // low 24 bits pick the side
+        return u < prob[slot] ? (uint32_t)slot : alias[slot];
+    }
+};
+
+}  // namespace
+
+extern "C" {
+
+int mggcn_gen_graph_begin(int64_t n_raw, int64_t target_directed_edges, int degree_model,
+                          double gamma, int64_t max_deg, uint64_t seed, int permute,
+                          mggcn_gen_t **out, int64_t *n_padded, int64_t *nnz) {
+    if (n_raw <= 0 || target_directed_edges < 0 || !out || !n_padded || !nnz)
+        return fail(MGGCN_E_INVALID, "bad argument");
+    const int64_t n = (n_raw + 7) / 8 * 8;
+    if (n > 0xFFFFFFFFll) return fail(MGGCN_E_UNSUPPORTED, "more than 2^32 vertices");
+    const int64_t E = target_directed_edges / 2;  // undirected samples; each yields two entries
+
+    alias_table tab;
+    if (degree_model == 1) {
+        // Chung-Lu weights w_i = (i + i0)^(-a), a = 1/(gamma-1); i0 set so that the heaviest
+        // vertex has expected degree max_deg.
+        const double a = 1.0 / std::max(1e-3, gamma - 1.0);
+        auto top_degree = [&](double i0) {
+            // fixed 64Ki blocks summed in block order: the same value for any thread count
+            const int64_t nb = (n_raw + 65535) / 65536;
+            std::vector<double> part((size_t)nb);
+#pragma omp parallel for schedule(static)
+            for (int64_t b = 0; b < nb; ++b) {
+                double s = 0;
+                const int64_t hi_i = std::min<int64_t>(n_raw, (b + 1) * 65536);
+                for (int64_t i = b * 65536; i < hi_i; ++i) s += std::pow((double)i + i0, -a);
+                part[b] = s;
+            }
+            double W = 0;
+            for (double s : part) W += s;
+            return 2.0 * (double)E * std::pow(i0, -a) / W;
+        };
+        double lo = 1e-3, hi = (double)n_raw;
+        if (max_deg <= 0) max_deg = n_raw / 10;
+        for (int it = 0; it < 60; ++it) {
+            double mid = std::sqrt(lo * hi);
+            (top_degree(mid) > (double)max_deg ? lo : hi) = mid;
+        }
+        const double i0 = std::sqrt(lo * hi);
+        std::vector<double> w((size_t)n_raw);
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n_raw; ++i) w[i] = std::pow((double)i + i0, -a);
+        tab.build(w);
+    } else if (degree_model != 0) {
+        return fail(MGGCN_E_INVALID, "unknown degree model %d", degree_model);
+    }
+    const std::vector<uint32_t> perm = make_perm(n, permute ? (seed ? seed : 1) : 0);
+
+    auto endpoints = [&](int64_t k, uint32_t &u, uint32_t &v) {
+        uint64_t hu = hash2(seed, 2 * (uint64_t)k), hv = hash2(seed, 2 * (uint64_t)k + 1);
+        if (degree_model == 1) {
+            u = tab.sample(hu);
+            v = tab.sample(hv);
+        } else {
+            u = (uint32_t)(((hu >> 32) * (uint64_t)n_raw) >> 32);
+            v = (uint32_t)(((hv >> 32) * (uint64_t)n_raw) >> 32);
+        }
+        u = perm[u];
+        v = perm[v];
+    };
+
+    // pass 1: degrees (both directions); self pairs are dropped, the self-loop is added later
+    std::vector<std::atomic<uint32_t>> deg((size_t)n);
+    for (auto &d : deg) d.store(0, std::memory_order_relaxed);
+#pragma omp parallel for schedule(static)
+    for (int64_t k = 0; k < E; ++k) {
+        uint32_t u, v;
+        endpoints(k, u, v);
+        if (u == v) continue;
+        deg[u].fetch_add(1, std::memory_order_relaxed);
+        deg[v].fetch_add(1, std::memory_order_relaxed);
+    }
+    std::vector<uint64_t> start((size_t)n + 1, 0);
+    for (int64_t i = 0; i < n; ++i) start[i + 1] = start[i] + deg[i].load(std::memory_order_relaxed);
+    std::vector<uint32_t> raw(start[n]);
+    std::vector<std::atomic<uint64_t>> cursor((size_t)n);
+    for (int64_t i = 0; i < n; ++i) cursor[i].store(start[i], std::memory_order_relaxed);
+    // pass 2: scatter (order inside a row is arbitrary here, fixed by the sort below)
+#pragma omp parallel for schedule(static)
+    for (int64_t k = 0; k < E; ++k) {
+        uint32_t u, v;
+        endpoints(k, u, v);
+        if (u == v) continue;
+        raw[cursor[u].fetch_add(1, std::memory_order_relaxed)] = v;
+        raw[cursor[v].fetch_add(1, std::memory_order_relaxed)] = u;
+    }
+    // pass 3: sort + dedup each row, insert the self-loop
+    std::vector<uint32_t> final_deg((size_t)n);
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t i = 0; i < n; ++i) {
+        uint32_t *b = raw.data() + start[i], *e = raw.data() + start[i + 1];
+        std::sort(b, e);
+        uint32_t *u = std::unique(b, e);
+        final_deg[i] = (uint32_t)(u - b) + 1;  // + self-loop (self pairs were never stored)
+    }
+    auto *g = new (std::nothrow) mggcn_gen;
+    if (!g) return fail(MGGCN_E_NOMEM, "out of memory");
+    g->n = n;
+    g->rowptr.assign((size_t)n + 1, 0);
+    for (int64_t i = 0; i < n; ++i) g->rowptr[i + 1] = g->rowptr[i] + final_deg[i];
+    g->colidx.resize(g->rowptr[n]);
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t i = 0; i < n; ++i) {
+        const uint32_t *b = raw.data() + start[i];
+        const uint32_t cnt = final_deg[i] - 1;
+        uint32_t *o = g->colidx.data() + g->rowptr[i];
+        uint32_t k = 0;
+        while (k < cnt && b[k] < (uint32_t)i) { *o++ = b[k]; ++k; }
+        *o++ = (uint32_t)i;
+        while (k < cnt) { *o++ = b[k]; ++k; }
+    }
+    *out = g;
+    *n_padded = n;
+    *nnz = (int64_t)g->rowptr[n];
+    return MGGCN_OK;
+}
+
+int mggcn_gen_graph_finish(mggcn_gen_t *g, uint64_t *rowptr, uint32_t *colidx, float *vals) {
+    if (!g) return fail(MGGCN_E_INVALID, "null generator");
+    if (rowptr) std::copy(g->rowptr.begin(), g->rowptr.end(), rowptr);
+    const int64_t nnz = (int64_t)g->rowptr[g->n];
+    if (colidx) {
+#pragma omp parallel for schedule(static)
+        for (int64_t e = 0; e < nnz; ++e) colidx[e] = g->colidx[e];
+    }
+    if (vals) {
+#pragma omp parallel for schedule(static)
+        for (int64_t e = 0; e < nnz; ++e) vals[e] = 1.0f;
+    }
+    delete g;
+    return MGGCN_OK;
+}
+
+int mggcn_gen_features(int64_t n_raw, int64_t n_padded, int64_t f_raw, int64_t f_padded,
+                       uint64_t seed, int permute, float *out) {
+    if (!out || n_raw > n_padded || f_raw > f_padded) return fail(MGGCN_E_INVALID, "bad argument");
+    const std::vector<uint32_t> perm = make_perm(n_padded, permute ? (seed ? seed : 1) : 0);
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n_padded; ++i) {
+        float *row = out + (size_t)perm[i] * f_padded;
+        for (int64_t j = 0; j < f_padded; ++j) {
+            if (i < n_raw && j < f_raw)
+                row[j] = (float)(2.0 * u01(hash2(seed ^ 0x46454154ull, (uint64_t)i * f_raw + j)) - 1.0);
+            else
+                row[j] = 0.f;
+        }
+    }
+    return MGGCN_OK;
+}
+
+int mggcn_gen_labels(int64_t n_raw, int64_t n_padded, int num_classes, uint64_t seed, int permute,
+                     int32_t *out) {
+    if (!out || n_raw > n_padded || num_classes <= 0) return fail(MGGCN_E_INVALID, "bad argument");
+    const std::vector<uint32_t> perm = make_perm(n_padded, permute ? (seed ? seed : 1) : 0);
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n_padded; ++i)
+        out[perm[i]] = i < n_raw ? (int32_t)(hash2(seed ^ 0x4C41424Cull, (uint64_t)i) % (uint64_t)num_classes) : 0;
+    return MGGCN_OK;
+}
+
+int mggcn_init_weights(int64_t rows, int64_t cols, float gain, float *out) {
+    if (!out || rows <= 0 || cols <= 0) return fail(MGGCN_E_INVALID, "bad argument");
+    // same engine, seed and distribution types as dn_matrix::init (src/matrix.hpp:539-545) so the
+    // libstdc++ stream is reproduced draw for draw
+    std::default_random_engine gen(99);
+    gain *= std::sqrt(3.0 / rows);
+    std::uniform_real_distribution<float> uni(-gain, gain);
+    for (int64_t i = 0; i < rows * cols; ++i) out[i] = uni(gen);
+    return MGGCN_OK;
+}
+
+}  // extern "C"
