@@ -108,7 +108,7 @@ MGGCN_API int mggcn_spmm_plan_create_i64(int64_t rows, const uint64_t *rowptr_ho
                                          int split_nnz, mggcn_spmm_plan_t **out);
 MGGCN_API size_t mggcn_spmm_plan_workspace_bytes(const mggcn_spmm_plan_t *plan, int F);
 MGGCN_API void mggcn_spmm_plan_destroy(mggcn_spmm_plan_t *plan);
-/* Tuning knobs for experiments ("unroll", "threads", "policy"); a negative value only queries.
+/* Tuning knobs for experiments ("unroll", "threads", "policy", "split"); a negative value only queries.
  * Returns the old value or MGGCN_E_INVALID for an unknown key. */
 MGGCN_API int mggcn_tune(const char *key, int value);
 
@@ -315,6 +315,8 @@ MGGCN_API int mggcn_engine_set(mggcn_engine_t *e, const char *name, const float 
 /* Timers in the reference's CSV schema "<name>:<ms>\n" (src/matrix.hpp:149-157). */
 MGGCN_API int mggcn_engine_dump_timers(mggcn_engine_t *e, const char *prefix, char *buf,
                                        size_t cap, size_t *written);
+/* Switches between graph replay (the product path) and eager execution with named timers. */
+MGGCN_API int mggcn_engine_set_mode(mggcn_engine_t *e, int use_graph, int timers);
 MGGCN_API int64_t mggcn_engine_launches_per_epoch(mggcn_engine_t *e);
 MGGCN_API void mggcn_engine_destroy(mggcn_engine_t *e);
 

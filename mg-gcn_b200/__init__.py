@@ -115,6 +115,7 @@ _SIGS = {
     "mggcn_engine_get": (C.c_int, [_vp, C.c_char_p, _vp, _sz, C.POINTER(_sz)]),
     "mggcn_engine_set": (C.c_int, [_vp, C.c_char_p, _vp, _sz]),
     "mggcn_engine_dump_timers": (C.c_int, [_vp, C.c_char_p, _vp, _sz, C.POINTER(_sz)]),
+    "mggcn_engine_set_mode": (C.c_int, [_vp, _i32, _i32]),
     "mggcn_engine_launches_per_epoch": (_i64, [_vp]),
     "mggcn_engine_destroy": (None, [_vp]),
     "mggcn_bcast_stage_f32": (C.c_int, [_vp, _vp, _vp, _vp, _sz, _i32]),
@@ -527,6 +528,9 @@ class Engine:
         buf = (C.c_char * (n.value + 1))()
         check(lib().mggcn_engine_dump_timers(self.handle, prefix.encode(), buf, n.value + 1, C.byref(n)))
         return bytes(buf).rstrip(b"\0").decode()
+
+    def set_mode(self, use_graph=False, timers=False):
+        check(lib().mggcn_engine_set_mode(self.handle, int(use_graph), int(timers)))
 
     @property
     def launches_per_epoch(self):

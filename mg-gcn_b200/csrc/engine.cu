@@ -935,6 +935,14 @@ int mggcn_engine_dump_timers(mggcn_engine_t *e, const char *prefix, char *buf, s
     return MGGCN_OK;
 }
 
+int mggcn_engine_set_mode(mggcn_engine_t *e, int use_graph, int timers) {
+    if (!e) return fail(MGGCN_E_INVALID, "null engine");
+    TRY(mggcn_engine_sync(e));
+    e->use_graph = use_graph != 0;
+    e->timers_on = timers != 0 && !e->use_graph;
+    return MGGCN_OK;
+}
+
 int64_t mggcn_engine_launches_per_epoch(mggcn_engine_t *e) { return e ? e->launches_per_epoch : 0; }
 
 void mggcn_engine_destroy(mggcn_engine_t *e) {

@@ -55,9 +55,10 @@ struct mggcn_spmm_plan {
 
 namespace {
 
-int g_unroll = 8;     // gathers in flight per lane (4 or 8)
-int g_threads = 128;  // CTA size
+int g_unroll = 4;     // gathers in flight per lane (4 or 8)
+int g_threads = 64;   // CTA size
 int g_policy = 1;     // 1: L2 evict_last for B, evict_first for the CSR stream; 0: plain loads
+int g_split = 0;      // row-split threshold of new plans; 0 = chosen from the matrix (see plan_create)
 
 struct spmm_args {
     const spmm_item *items;  // null: natural order, one item per row from rowptr
@@ -446,7 +447,17 @@ template <typename idx_t>
 int plan_create(int64_t rows, const idx_t *rowptr, int split_nnz, mggcn_spmm_plan_t **out) {
     if (!out || rows < 0 || (rows > 0 && !rowptr)) return fail(MGGCN_E_INVALID, "bad argument");
     if (rows > 0xFFFFFFFFll) return fail(MGGCN_E_UNSUPPORTED, "more than 2^32 rows in one block");
-    if (split_nnz <= 0) split_nnz = 2048;
+    if (split_nnz <= 0) split_nnz = g_split;
+    if (split_nnz <= 0) {
+        // A warp works through its item with a fixed number of gathers in flight, so one long item
+        // is a serial chain of L2 round trips: keep every item well below the kernel's duration.
+        // Aim at >= 2 items per resident warp slot (148 SMs x 32 warps), between 64 and 2048 entries
+        // (measured on B200: reddit-shape whole matrix best at 2048, its 8x8 blocks at 256-512).
+        const uint64_t nnz = rows > 0 ? (uint64_t)rowptr[rows] - (uint64_t)rowptr[0] : 0;
+        uint64_t s = nnz / (148ull * 32 * 2);
+        s = (s + 31) / 32 * 32;
+        split_nnz = (int)std::min<uint64_t>(2048, std::max<uint64_t>(64, s));
+    }
     if (split_nnz < 32) split_nnz = 32;
     auto *p = new (std::nothrow) mggcn_spmm_plan;
     if (!p) return fail(MGGCN_E_NOMEM, "out of memory");
@@ -551,6 +562,7 @@ int mggcn_tune(const char *key, int value) {
     if (!strcmp(key, "unroll")) slot = &g_unroll;
     else if (!strcmp(key, "threads")) slot = &g_threads;
     else if (!strcmp(key, "policy")) slot = &g_policy;
+    else if (!strcmp(key, "split")) slot = &g_split;
     if (!slot) return fail(MGGCN_E_INVALID, "unknown tuning key %s", key);
     const int old = *slot;
     if (slot == &g_threads && (value < 32 || value > 256 || value % 32)) return fail(MGGCN_E_INVALID, "threads must be 32..256");

@@ -1,0 +1,100 @@
+"""The epoch engine (gcn / dist_gcn mirror) against the oracle model on BASELINE.json config 1
+(4,096-node synthetic graph, avg deg 16, F = 64) and a deeper / SpMM-first variant.
+
+Bars (north_star): per-layer outputs and gradients within 1e-5 relative, training loss within 1e-4
+over 10 epochs, partitioning bit-exact (tests/test_host.py)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def build(mg, orc, shape, hidden, world=1, rank=0, scale=1.0, **kw):
+    A, X, Y, C = mg.generate(shape, seed=1, scale=scale)
+    sizes = [X.shape[1]] + list(hidden) + [mg.pad_classes(C, world)]
+    eng, A_T = mg.build_rank_engine(A, sizes, world=world, rank=rank, **kw)
+    ref = orc.Gcn(sizes, A.n, (A_T.rowptr, A_T.colidx, A_T.vals), (A.rowptr, A.colidx, A.vals), P=1,
+                  exact_grads=kw.get("exact_grads", False))
+    return eng, ref, A, X, Y, sizes
+
+
+def rel(a, b):
+    a = np.asarray(a, np.float64).ravel(); b = np.asarray(b, np.float64).ravel()
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+@pytest.mark.parametrize("shape,hidden,exact", [("oracle4k", [64], False), ("oracle4k", [64, 64, 64], False),
+                                                ((3000, 3000 * 20, 8, 12, 0, 0.0, 0), [32, 32], False),
+                                                ((3000, 3000 * 20, 8, 12, 0, 0.0, 0), [32, 32], True),
+                                                ((2500, 2500 * 30, 100, 47, 1, 2.5, 300), [128, 128, 128], False)])
+def test_layers_grads_and_loss_curve(mg, orc, cuda, shape, hidden, exact):
+    eng, ref, A, X, Y, sizes = build(mg, orc, shape, hidden, exact_grads=exact)
+    eng.set_inputs(X, Y)
+    L = len(sizes) - 1
+    for epoch in range(10):
+        ls, cs = eng.train_forward()
+        rloss, racc = ref.train_forward(X, Y)
+        assert abs(ls / A.n - rloss) <= 1e-4, (epoch, ls / A.n, rloss)
+        assert abs(cs / A.n - racc) <= 2.0 / A.n + 1e-6
+        if epoch in (0, 9):
+            for l in range(L - 1):  # the last layer's buffer holds the loss gradient by now
+                assert rel(eng.get(f"H{l}"), ref.tensor(f"H{l}")) <= 1e-5, (epoch, l)
+        eng.backward(); ref.backward()
+        if epoch in (0, 9):
+            for l in range(L):
+                assert rel(eng.get(f"GW{l}"), ref.tensor(f"GW{l}")) <= 2e-5, (epoch, l)
+                assert rel(eng.get(f"Gb{l}"), ref.tensor(f"Gb{l}")) <= 2e-5, (epoch, l)
+        eng.adam_update(); ref.adam_update()
+        # Adam divides by sqrt(v)+eps: where a gradient entry is itself rounding noise (|g| ~ eps) the
+        # step direction is arbitrary, so weights are compared at a fraction of the step size lr=1e-2
+        for l in range(L):
+            assert np.abs(eng.get(f"W{l}") - ref.tensor(f"W{l}")).max() <= 2e-3 * (epoch + 1), (epoch, l)
+    eng.close()
+
+
+def test_initial_weights_are_the_reference_stream(mg, orc, cuda):
+    eng, ref, *_ = build(mg, orc, "oracle4k", [64])
+    for l in range(2):
+        assert np.array_equal(eng.get(f"W{l}"), ref.tensor(f"W{l}"))
+        assert np.array_equal(eng.get(f"b{l}"), ref.tensor(f"b{l}"))
+    eng.close()
+
+
+def test_graph_replay_equals_eager(mg, orc, cuda):
+    """use_graph captures the whole epoch once; replays must reproduce eager execution bit for bit."""
+    out = []
+    for use_graph in (False, True):
+        A, X, Y, C = mg.generate("oracle4k", seed=1)
+        sizes = [X.shape[1], 64, 64, C]
+        eng, _ = mg.build_rank_engine(A, sizes, use_graph=use_graph)
+        eng.set_inputs(X, Y)
+        losses = []
+        for _ in range(5):
+            eng.epoch()
+            losses.append(eng.loss()[0])
+        out.append((losses, eng.get("W0"), eng.get("W2")))
+        assert eng.launches_per_epoch > 10
+        eng.close()
+    assert out[0][0] == out[1][0]
+    assert np.array_equal(out[0][1], out[1][1]) and np.array_equal(out[0][2], out[1][2])
+
+
+def test_timers_csv_schema(mg, orc, cuda):
+    A, X, Y, C = mg.generate("oracle4k", seed=1)
+    eng, _ = mg.build_rank_engine(A, [X.shape[1], 64, C], timers=True)
+    eng.set_inputs(X, Y)
+    eng.epoch()
+    txt = eng.timers("0_0_")
+    names = [l.split(":")[0] for l in txt.strip().splitlines()]
+    assert "0_0_0_0_matmul-spmm" in names and "0_0_2_loss-layer" in names and "0_0_adam-update" in names
+    assert all(float(l.split(":")[1]) >= 0 for l in txt.strip().splitlines())
+    eng.close()
+
+
+def test_state_errors(mg, cuda):
+    eng = mg.Engine([8, 4, 3], 16)
+    with pytest.raises(mg.MggcnError):
+        eng.epoch()  # adjacency not set
+    with pytest.raises(mg.MggcnError):
+        eng.backward()
+    eng.close()

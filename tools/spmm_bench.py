@@ -1,0 +1,91 @@
+"""SpMM micro-benchmark on one GPU: our kernel (knob sweep) vs cuSPARSE (through torch.sparse, harness
+only) on a BASELINE.json shape.  Prints one JSON line per measurement.  Usage:
+  python tools/spmm_bench.py --shape reddit --F 128 [--sweep] [--blocks P]"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from __graft_entry__ import load_package  # noqa: E402
+
+
+def timeit(fn, iters=5, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record(); torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    return float(np.median(ts)), float(np.min(ts))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--shape", default="reddit")
+    ap.add_argument("--F", type=int, nargs="+", default=[128])
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--blocks", type=int, default=1, help="P: time the diagonal block (0,0) of a P x P split")
+    ap.add_argument("--cusparse", action="store_true")
+    ap.add_argument("--splits", type=int, nargs="*", default=[])
+    ap.add_argument("--unroll", type=int, default=4)
+    ap.add_argument("--threads", type=int, default=64)
+    args = ap.parse_args()
+    mg = load_package()
+    t0 = time.time()
+    A, _, _, _ = mg.generate(args.shape, seed=1, features=False, scale=args.scale)
+    A.normalize(True)
+    AT = A.transpose()
+    if args.blocks > 1:
+        cuts = mg.row_cuts(AT.n, args.blocks)
+        AT = AT.block_rows(cuts, cuts, only_row=0)[0]
+    n, m, nnz = AT.n, AT.m, AT.nnz
+    print(json.dumps({"shape": args.shape, "rows": n, "cols": m, "nnz": nnz, "prep_s": round(time.time() - t0, 1)}), flush=True)
+    rpt = torch.from_numpy(AT.rowptr.astype(np.uint32).view(np.int32)).cuda()
+    cit = torch.from_numpy(AT.colidx.view(np.int32)).cuda()
+    vat = torch.from_numpy(AT.vals).cuda()
+    plan = mg.SpmmPlan(AT.rowptr.astype(np.uint32))
+    for F in args.F:
+        ld = (F + 3) // 4 * 4
+        B = (torch.rand((m, ld), device="cuda") * 2 - 1)
+        Cm = torch.empty((n, ld), device="cuda")
+        b_alg = nnz * 8 + (n + 1) * 4 + m * F * 4 + n * F * 4
+        b_gather = nnz * F * 4 + nnz * 8 + n * F * 4
+
+        def report(tag, med, mn, **kw):
+            print(json.dumps({"tag": tag, "F": F, "ms_med": round(med, 4), "ms_min": round(mn, 4),
+                              "alg_GBps": round(b_alg / mn / 1e6, 1), "gather_GBps": round(b_gather / mn / 1e6, 1),
+                              "GFLOPs": round(2 * nnz * F / mn / 1e6, 1), **kw}), flush=True)
+
+        configs = [(args.unroll, args.threads, 1, True)]
+        if args.sweep:
+            configs = [(u, t, p, pl) for u in (4, 8) for t in (64, 128, 256) for p in (0, 1) for pl in (True,)] + [(8, 128, 1, False)]
+        for unroll, threads, policy, use_plan in configs:
+            mg.lib().mggcn_tune(b"unroll", unroll)
+            mg.lib().mggcn_tune(b"threads", threads)
+            mg.lib().mggcn_tune(b"policy", policy)
+            med, mn = timeit(lambda: mg.spmm(rpt, cit, vat, B, Cm, cols=m, F=F, plan=plan if use_plan else None))
+            report("ours", med, mn, unroll=unroll, threads=threads, policy=policy, plan=use_plan)
+        for sp in args.splits:
+            pl = mg.SpmmPlan(AT.rowptr.astype(np.uint32), split_nnz=sp)
+            med, mn = timeit(lambda: mg.spmm(rpt, cit, vat, B, Cm, cols=m, F=F, plan=pl))
+            report("ours-split", med, mn, split=sp)
+        if args.cusparse:
+            S = torch.sparse_csr_tensor(rpt.to(torch.int32), cit, vat, size=(n, m))
+            Bc = B[:, :F].contiguous()
+            med, mn = timeit(lambda: torch.sparse.mm(S, Bc))
+            report("cusparse(torch.sparse.mm)", med, mn)
+            ref = torch.sparse.mm(S, Bc)
+            mg.spmm(rpt, cit, vat, B, Cm, cols=m, F=F, plan=plan)
+            print(json.dumps({"max_abs_diff_vs_cusparse": float((ref - Cm[:, :F]).abs().max())}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
