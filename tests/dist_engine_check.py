@@ -1,0 +1,103 @@
+"""Run under torchrun (one process per GPU): the multi-GPU engine against the oracle's dist_gcn
+restatement at equal P (class padding and stage order depend on P).
+  torchrun --nproc-per-node 2 tests/dist_engine_check.py --comm p2p [--graph] [--shape oracle4k]
+Exit code 0 = parity green on every rank."""
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from __graft_entry__ import load_package  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--comm", default="p2p")
+    ap.add_argument("--graph", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--epochs", type=int, default=10)
+    ap.add_argument("--hidden", type=int, nargs="+", default=[64, 64])
+    args = ap.parse_args()
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    mg = load_package()
+    from oracle import oracle as orc
+    A, X, Y, C = mg.generate("oracle4k", seed=1)
+    N = A.n
+    sizes = [X.shape[1]] + args.hidden + [mg.pad_classes(C, world)]
+    comm = mg.COMM_P2P if args.comm == "p2p" else mg.COMM_NCCL
+    nccl_id = None
+    if comm == mg.COMM_NCCL:
+        import ctypes
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            buf = (ctypes.c_char * 128)()
+            mg.check(mg.lib().mggcn_nccl_unique_id(buf))
+            idt.copy_(torch.frombuffer(bytearray(bytes(buf)), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        nccl_id = bytes(idt.cpu().numpy().tobytes())
+    eng, A_T = mg.build_rank_engine(A, sizes, world=world, rank=rank, device=local, use_graph=args.graph,
+                                    nccl_id=nccl_id, comm=comm, overlap=not args.no_overlap)
+    if comm == mg.COMM_P2P:
+        ht = torch.frombuffer(bytearray(eng.comm_handle()), dtype=torch.uint8).cuda()
+        allh = [torch.empty_like(ht) for _ in range(world)]
+        dist.all_gather(allh, ht)
+        eng.comm_connect([bytes(t.cpu().numpy().tobytes()) for t in allh])
+    cuts = mg.row_cuts(N, world)
+    r0, r1 = int(cuts[rank]), int(cuts[rank + 1])
+    eng.set_inputs(np.ascontiguousarray(X[r0:r1]), np.ascontiguousarray(Y[r0:r1]))
+    ref = orc.Gcn(sizes, N, (A_T.rowptr, A_T.colidx, A_T.vals), (A.rowptr, A.colidx, A.vals), P=world, cuts=cuts)
+    L = len(sizes) - 1
+    worst = 0.0
+
+    def rel(a, b):
+        return float(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64)).max() / max(np.abs(b).max(), 1e-30))
+
+    for epoch in range(args.epochs):
+        if args.graph:
+            eng.epoch()
+            ls, cs = eng.loss()
+        else:
+            ls, cs = eng.train_forward()
+        t = torch.tensor([ls, cs], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        rloss, racc = ref.train_forward(X, Y)
+        loss = float(t[0]) / N
+        assert abs(loss - rloss) <= 1e-4, (epoch, loss, rloss)
+        if not args.graph:
+            for l in range(L - 1):
+                h = eng.get(f"H{l}").reshape(r1 - r0, -1)
+                want = ref.tensor(f"H{l}").reshape(N, -1)[r0:r1]
+                worst = max(worst, rel(h, want))
+                assert rel(h, want) <= 1e-5, (epoch, l, rel(h, want))
+            eng.backward()
+        ref.backward()
+        if not args.graph:
+            for l in range(L):
+                for nm in (f"GW{l}", f"Gb{l}"):
+                    assert rel(eng.get(nm), ref.tensor(nm)) <= 2e-5, (epoch, nm, rel(eng.get(nm), ref.tensor(nm)))
+            eng.adam_update()
+        ref.adam_update()
+        if rank == 0:
+            print(f"epoch {epoch} loss {loss:.6f} oracle {rloss:.6f}", flush=True)
+    eng.sync()
+    w0 = eng.get("W0")
+    t = torch.from_numpy(w0).cuda()
+    t0 = t.clone()
+    dist.broadcast(t0, 0)
+    assert torch.equal(t, t0), "replicated weights diverged between ranks"
+    eng.close()
+    dist.barrier()
+    if rank == 0:
+        print(f"dist check ok: world={world} comm={args.comm} graph={args.graph} worst layer rel err {worst:.2e}", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -98,3 +98,21 @@ def test_state_errors(mg, cuda):
     with pytest.raises(mg.MggcnError):
         eng.backward()
     eng.close()
+
+
+@pytest.mark.parametrize("comm,graph", [("nccl", False), ("p2p", False), ("p2p", True), ("nccl", True)])
+def test_two_gpu_engine_matches_oracle(cuda, comm, graph):
+    """One process per GPU (torchrun), world 2: staged exchange + SpMM, gradient reduction, Adam."""
+    import os
+    import subprocess
+    import sys
+    if cuda.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29611", os.path.join(root, "tests", "dist_engine_check.py"), "--comm", comm]
+    if graph:
+        cmd.append("--graph")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert "dist check ok" in r.stdout
