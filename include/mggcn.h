@@ -291,8 +291,12 @@ MGGCN_API int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which,
                                          const uint64_t *const *blk_rowptr,
                                          const uint32_t *const *blk_colidx,
                                          const float *const *blk_vals);
-/* Host -> device copy of this rank's rows of X (n_local x F_in) and Y (n_local); async on the
- * engine's copy stream when `async` != 0 (pinned memory expected). */
+/* Host -> device copy of this rank's rows of X (n_local x F_in) and Y (n_local).
+ *  async = 0: copy on the compute stream, return when done;
+ *  async = 1: enqueue on the compute stream (ordered after the epochs already queued), return at once;
+ *  async = 2: prefetch -- copy into shadow buffers on the engine's copy stream, concurrent with the
+ *             epoch the compute stream is running; the next epoch / train_forward swaps them in
+ *             (device to device) before it starts.  Pinned host memory expected for 1 and 2. */
 MGGCN_API int mggcn_engine_set_inputs(mggcn_engine_t *e, const float *X_host,
                                       const int32_t *Y_host, int async);
 MGGCN_API int mggcn_engine_train_forward(mggcn_engine_t *e);

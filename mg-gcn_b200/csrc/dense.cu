@@ -3,14 +3,25 @@
 // element-wise kernels the reference launches separately, the fused softmax-cross-entropy loss and
 // the fused Adam step.  Reference anchors are cited per entry point in include/mggcn.h.
 //
-// The tensor-core (tcgen05 / TMEM / TMA) form of the transform lives in gemm_tc.cu; this file is
-// the FP32-exact form every parity test is pinned on (the reference's cublasSgemm is FP32 SIMT too,
-// src/cuda_utils.hpp:168-171).
+// The tensor-core (tcgen05 / TMEM / TMA, 3xTF32) form of the transform lives in gemm_tc.cu and is
+// taken whenever the operands are 16-byte aligned; this file keeps the FP32 SIMT form for
+// unaligned / tiny products (the reference's cublasSgemm is FP32 SIMT too, src/cuda_utils.hpp:168-171).
 #include <algorithm>
 
 #include "common.hpp"
 
 using namespace mggcn;
+
+namespace mggcn {
+// gemm_tc.cu: tcgen05 / TMEM / TMA form (3xTF32), used whenever the operands are 16-byte aligned
+bool gemm_tc_eligible(int64_t M, int64_t N, int64_t K, const float *A, int64_t lda, const float *B, int64_t ldb);
+size_t gemm_tc_workspace_bytes(int ta, int64_t M, int64_t N, int64_t K);
+int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, float alpha, const float *A, int64_t lda,
+            const float *B, int64_t ldb, float beta, float *C, int64_t ldc, const mggcn_epilogue &epi, void *ws,
+            size_t ws_bytes);
+int launch_splitk_reduce(cudaStream_t st, const float *part, int nz, int64_t M, int64_t N, float *C, int64_t ldc,
+                         float alpha, float beta, const mggcn_epilogue &epi);
+}  // namespace mggcn
 
 namespace {
 
@@ -393,12 +404,22 @@ __global__ void adam_kernel(size_t n, float *p, float *g, float *m, float *v, fl
 
 }  // namespace
 
+namespace mggcn {
+int launch_splitk_reduce(cudaStream_t st, const float *part, int nz, int64_t M, int64_t N, float *C, int64_t ldc,
+                         float alpha, float beta, const mggcn_epilogue &epi) {
+    splitk_reduce_kernel<<<ew_grid((size_t)(M * N)), 256, 0, st>>>(part, nz, M, N, C, ldc, alpha, beta, epi);
+    MGGCN_LAUNCH_CHECK();
+    return MGGCN_OK;
+}
+}  // namespace mggcn
+
 extern "C" {
 
 size_t mggcn_gemm_workspace_bytes(int ta, int tb, int64_t M, int64_t N, int64_t K) {
     (void)tb;
     const int nz = splitk_slices(ta, M, N, K);
-    return nz > 1 ? (size_t)nz * (size_t)M * (size_t)N * sizeof(float) : 0;
+    const size_t simt = nz > 1 ? (size_t)nz * (size_t)M * (size_t)N * sizeof(float) : 0;
+    return std::max(simt, gemm_tc_workspace_bytes(ta, M, N, K));
 }
 
 int mggcn_gemm_f32(mggcn_stream_t stream, int ta, int tb, int64_t M, int64_t N, int64_t K, float alpha,
@@ -415,6 +436,8 @@ int mggcn_gemm_f32(mggcn_stream_t stream, int ta, int tb, int64_t M, int64_t N, 
     g.alpha = alpha; g.beta = beta;
     if (epi) g.epi = *epi;
     if (g.epi.kind == MGGCN_EPI_LEAKY_RELU_BWD && !g.epi.aux) return fail(MGGCN_E_INVALID, "LEAKY_RELU_BWD epilogue needs aux");
+    if (gemm_tc_eligible(M, N, K, A, lda, B, ldb))
+        return gemm_tc(st, ta, tb, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, g.epi, ws, ws_bytes);
     g.vecA = lda % 4 == 0 && (reinterpret_cast<uintptr_t>(A) & 15) == 0;
     g.vecB = ldb % 4 == 0 && (reinterpret_cast<uintptr_t>(B) & 15) == 0;
     g.vecC = ldc % 4 == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0;

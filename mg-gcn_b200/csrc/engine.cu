@@ -223,6 +223,11 @@ struct mggcn_engine {
 
     // events (created once)
     cudaEvent_t ev_ready = nullptr, ev_done = nullptr, ev_join = nullptr;
+    // input prefetch (set_inputs async == 2): shadow copies filled on the copy stream while an epoch runs
+    float *X_shadow = nullptr;
+    int32_t *Y_shadow = nullptr;
+    cudaEvent_t ev_pref = nullptr, ev_swap = nullptr;
+    bool pref_x = false, pref_y = false, swap_recorded = false;
     std::vector<cudaEvent_t> ev_xfer, ev_spmm;
 
     // graph
@@ -469,6 +474,20 @@ int adam(eng *e, float lr, float b1, float b2, float wd, float eps) {
                                              b1, b2, wd, eps, e->n_weights);
     MGGCN_LAUNCH_CHECK();
     TRY(timer_end(e, e->sc, tg));
+    return MGGCN_OK;
+}
+
+// Makes prefetched inputs current: ordered after the prefetch on the copy stream and after everything
+// already queued on the compute stream (the previous epoch's backward reads X).
+int swap_in_inputs(eng *e) {
+    if (!e->pref_x && !e->pref_y) return MGGCN_OK;
+    MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_pref, 0));
+    if (e->pref_x)
+        MGGCN_CUDA_TRY(cudaMemcpyAsync(e->X, e->X_shadow, (size_t)e->n * (size_t)e->ldX * 4, cudaMemcpyDeviceToDevice, e->sc));
+    if (e->pref_y) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y, e->Y_shadow, (size_t)e->n * 4, cudaMemcpyDeviceToDevice, e->sc));
+    MGGCN_CUDA_TRY(cudaEventRecord(e->ev_swap, e->sc));
+    e->swap_recorded = true;
+    e->pref_x = e->pref_y = false;
     return MGGCN_OK;
 }
 
@@ -719,6 +738,26 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
 int mggcn_engine_set_inputs(mggcn_engine_t *e, const float *X_host, const int32_t *Y_host, int async) {
     if (!e) return fail(MGGCN_E_INVALID, "null engine");
     TRY(set_dev(e));
+    if (async == 2) {
+        // prefetch: host -> shadow buffers on the copy stream, concurrent with whatever the compute stream
+        // is running; the next epoch / train_forward swaps them in (device-to-device) before it starts
+        if (!e->X_shadow) {
+            MGGCN_CUDA_TRY(cudaMalloc(&e->X_shadow, (size_t)e->n * (size_t)e->ldX * 4));
+            MGGCN_CUDA_TRY(cudaMemset(e->X_shadow, 0, (size_t)e->n * (size_t)e->ldX * 4));
+            MGGCN_CUDA_TRY(cudaMalloc(&e->Y_shadow, (size_t)e->n * 4));
+            MGGCN_CUDA_TRY(cudaEventCreateWithFlags(&e->ev_pref, cudaEventDisableTiming));
+            MGGCN_CUDA_TRY(cudaEventCreateWithFlags(&e->ev_swap, cudaEventDisableTiming));
+        }
+        if (e->swap_recorded) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->scopy, e->ev_swap, 0));  // WAR on the shadows
+        if (X_host)
+            MGGCN_CUDA_TRY(cudaMemcpy2DAsync(e->X_shadow, (size_t)e->ldX * 4, X_host, (size_t)e->sizes[0] * 4,
+                                             (size_t)e->sizes[0] * 4, (size_t)e->n, cudaMemcpyHostToDevice, e->scopy));
+        if (Y_host) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y_shadow, Y_host, (size_t)e->n * 4, cudaMemcpyHostToDevice, e->scopy));
+        MGGCN_CUDA_TRY(cudaEventRecord(e->ev_pref, e->scopy));
+        e->pref_x = e->pref_x || X_host;
+        e->pref_y = e->pref_y || Y_host;
+        return MGGCN_OK;
+    }
     // ordered after everything already queued on the compute stream (the previous epoch reads X)
     cudaStream_t st = e->sc;
     if (X_host)
@@ -786,6 +825,7 @@ int mggcn_engine_train_forward(mggcn_engine_t *e) {
     if (!e) return fail(MGGCN_E_INVALID, "null engine");
     TRY(check_ready(e));
     TRY(set_dev(e));
+    TRY(swap_in_inputs(e));
     begin_pass(e);
     TRY(forward(e));
     e->forward_done = true;
@@ -811,6 +851,7 @@ int mggcn_engine_epoch(mggcn_engine_t *e, float lr, float beta1, float beta2, fl
     if (!e) return fail(MGGCN_E_INVALID, "null engine");
     TRY(check_ready(e));
     TRY(set_dev(e));
+    TRY(swap_in_inputs(e));
     if (!e->use_graph) {
         const uint64_t before = mggcn_launch_count();
         TRY(epoch_body(e, lr, beta1, beta2, wd, eps));
@@ -970,6 +1011,10 @@ void mggcn_engine_destroy(mggcn_engine_t *e) {
     if (e->ev_ready) cudaEventDestroy(e->ev_ready);
     if (e->ev_done) cudaEventDestroy(e->ev_done);
     if (e->ev_join) cudaEventDestroy(e->ev_join);
+    if (e->ev_pref) cudaEventDestroy(e->ev_pref);
+    if (e->ev_swap) cudaEventDestroy(e->ev_swap);
+    if (e->X_shadow) cudaFree(e->X_shadow);
+    if (e->Y_shadow) cudaFree(e->Y_shadow);
     if (e->sm && e->sm != e->sc) cudaStreamDestroy(e->sm);
     if (e->sc) cudaStreamDestroy(e->sc);
     if (e->scopy) cudaStreamDestroy(e->scopy);

@@ -1,0 +1,621 @@
+// Tensor-core form of the dense transform for sm_100a: tcgen05.mma (kind::tf32) with TMEM
+// accumulators, TMA-fed shared-memory operand ring, 3xTF32 error compensation.
+//
+// Replaces cublasSgemm (FP32 SIMT, no TF32 math mode: src/cuda_utils.hpp:158-172) for the
+// H*W (+b, activation), G*W^T (+activation gradient) and X^T*G products of src/gcn.hpp:191-296.
+// The reference's result is an FP32-accurate product, and the parity bar is 1e-5 relative, so a
+// plain TF32 product (10-bit mantissa, ~1e-3) is not admissible.  Every operand x is split into
+//     hi = tf32(x),  lo = tf32(x - hi)
+// and the product is accumulated as  lo_a*hi_b + hi_a*lo_b + hi_a*hi_b  (the dropped lo*lo term is
+// 2^-22 relative).  Tensor-core accumulation chains are kept short: after `kgroup` k-blocks the
+// TMEM accumulator is drained into FP32 registers (round-to-nearest adds) by the epilogue warps,
+// so the rounding behaviour of the tensor-core adder never builds up over a long K (K is the number
+// of vertices in X^T*G).
+//
+// Structure (one persistent CTA per SM, 448 threads):
+//   warp 0      TMA producer: raw fp32 tiles of A and B -> smem (128-byte swizzle), mbarrier tx
+//   warps 2-5   splitters: raw tile -> hi (in place) + lo (sibling buffer), generic->async fence
+//   warp 1      MMA issuer (one lane): 3 x tcgen05.mma.kind::tf32 per 8-wide k step,
+//               tcgen05.commit frees the smem stage / publishes the TMEM accumulator
+//   warps 6-13  accumulate + epilogue: tcgen05.ld the 128 x BN accumulator (two warps per TMEM lane
+//               quarter, half of the columns each), add into registers; at the end of a tile alpha/beta,
+//               bias, LeakyReLU (forward or gradient), keep-mask, transposed through smem so that
+//               global accesses are float4 pieces of whole rows
+// Operand layouts: both the k-contiguous ("K-major") and the row-contiguous ("MN-major") form of
+// each operand are fed straight from the caller's row-major arrays -- no transposed copies.
+// Split-K (X^T*G): slice z of K writes its raw partial tile; the slices are added in z order by
+// splitk_reduce (deterministic, no atomics).
+#include <cuda.h>  // CUtensorMap and its enums; the encoder is resolved at run time (no -lcuda)
+
+#include <algorithm>
+#include <mutex>
+
+#include "common.hpp"
+
+using namespace mggcn;
+
+namespace mggcn {
+int g_gemm_tc = 1;       // 0: never use this path (mggcn_tune "gemm_tc")
+int g_gemm_kgroup = 2;   // k-blocks per tensor-core accumulation chain (mggcn_tune "gemm_kgroup")
+}  // namespace mggcn
+
+namespace {
+
+constexpr int BM = 128;          // tile rows (UMMA M, all 128 TMEM lanes)
+constexpr int BK = 32;           // fp32 per k-block = one 128-byte swizzle row
+constexpr int UK = 8;            // tf32 UMMA K
+constexpr int NTHREADS = 448;
+constexpr int SPLIT_WARP0 = 2, EPI_WARP0 = 6;
+constexpr uint32_t A_TILE_BYTES = BM * BK * 4;  // 16 KB
+constexpr int STG_LD = 20;       // epilogue staging row stride (floats): 16-byte aligned rows, conflict-free float4 access
+
+template <int BN>
+struct cfg {
+    static constexpr int STAGES = BN == 128 ? 3 : 4;
+    static constexpr uint32_t B_TILE_BYTES = BN * BK * 4;
+    static constexpr uint32_t STAGE_BYTES = 2 * A_TILE_BYTES + 2 * B_TILE_BYTES;
+    static constexpr uint32_t STG_BYTES = 8 * 32 * STG_LD * 4;
+    static constexpr uint32_t BAR_BYTES = 256;
+    static constexpr uint32_t SMEM_BYTES = STAGES * STAGE_BYTES + STG_BYTES + BAR_BYTES + 1024;
+    static constexpr int TMEM_COLS = 2 * BN;  // two accumulator stages (power of two: 128 / 256)
+};
+
+struct tc_args {
+    int64_t M, N, K;
+    float *C;
+    int64_t ldc;
+    float *part;       // split-K partials: nz x M x N
+    int nz;
+    int64_t kchunk;    // multiple of BK
+    int mt, nt;        // tiles along M, N
+    int kgroup;
+    float alpha, beta;
+    mggcn_epilogue epi;
+};
+
+// ---------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// Bounded wait (about 2 s of SM clock): a protocol bug traps instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (!done && (spin & 1023u) == 1023u) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 4000000000ll) {
+                printf("mggcn gemm_tc: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x,
+                       threadIdx.x, bar, parity);
+                __trap();
+            }
+        }
+    }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float *v) {
+    uint32_t *r = reinterpret_cast<uint32_t *>(v);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// shared-memory matrix descriptor, 128-byte swizzle (cute::UMMA::SmemDescriptor: start [0,14),
+// leading byte offset [16,30), stride byte offset [32,46), version=1 [46,48), layout=2 [61,64))
+// layout: 2 = SWIZZLE_128B (16-byte chunks, K-major operands), 1 = SWIZZLE_128B_BASE32B (32-byte chunks:
+// the only shared-memory layout the tensor core accepts for an MN-major 32-bit operand)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+    uint64_t d = (uint64_t)((addr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)(lbo_bytes >> 4) << 16;
+    d |= (uint64_t)(sbo_bytes >> 4) << 32;
+    d |= 1ull << 46;
+    d |= (uint64_t)layout << 61;
+    return d;
+}
+
+__device__ __forceinline__ float epi_apply(float x, const mggcn_epilogue &e, int64_t row, int64_t col, float bias) {
+    x += bias;
+    if (e.kind == MGGCN_EPI_LEAKY_RELU) {
+        const float ax = e.slope * x;
+        x = x > ax ? x : ax;
+    } else if (e.kind == MGGCN_EPI_LEAKY_RELU_BWD) {
+        const float z = __ldg(e.aux + row * e.ld_aux + col);
+        x = z > 0.f ? x : e.slope * x;
+    }
+    if (e.keep_mask) x = e.keep_mask[row * e.ld_mask + col] ? x * e.keep_scale : 0.f;
+    return x;
+}
+
+// ---------------------------------------------------------------------------------------------
+// A_MN: A is stored K x M (m contiguous, the reference's A_T flag);  else M x K.
+// B_MN: B is stored K x N (n contiguous, the plain case);            else N x K (the B_T flag).
+// ---------------------------------------------------------------------------------------------
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(NTHREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const tc_args g) {
+    using C = cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t *gen_base = smem_raw + (base - smem_u32(smem_raw));
+    const uint32_t stg_addr = base + C::STAGES * C::STAGE_BYTES;
+    float *stg = reinterpret_cast<float *>(gen_base + C::STAGES * C::STAGE_BYTES);
+    const uint32_t bars = stg_addr + C::STG_BYTES;
+    // barrier table (8 bytes each): full[S], conv[S], empty[S], tfull[2], tempty[2]; then the TMEM pointer
+    auto bar_full = [&](int s) { return bars + 8u * s; };
+    auto bar_conv = [&](int s) { return bars + 8u * (C::STAGES + s); };
+    auto bar_empty = [&](int s) { return bars + 8u * (2 * C::STAGES + s); };
+    auto bar_tfull = [&](int a) { return bars + 8u * (3 * C::STAGES + a); };
+    auto bar_tempty = [&](int a) { return bars + 8u * (3 * C::STAGES + 2 + a); };
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(gen_base + C::STAGES * C::STAGE_BYTES +
+                                                                         C::STG_BYTES + 8 * (3 * C::STAGES + 4));
+    auto a_hi = [&](int s) { return base + s * C::STAGE_BYTES; };
+    auto a_lo = [&](int s) { return base + s * C::STAGE_BYTES + A_TILE_BYTES; };
+    auto b_hi = [&](int s) { return base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES; };
+    auto b_lo = [&](int s) { return base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES + C::B_TILE_BYTES; };
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < C::STAGES; ++s) {
+            mbar_init(bar_full(s), 1);
+            mbar_init(bar_conv(s), 4);
+            mbar_init(bar_empty(s), 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(bar_tfull(a), 1);
+            mbar_init(bar_tempty(a), 8);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         smem_u32(const_cast<uint32_t *>(tmem_slot))),
+                     "r"((uint32_t)C::TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int64_t tiles_mn = (int64_t)g.mt * g.nt;
+    const int64_t total = tiles_mn * g.nz;
+    const int64_t kb_all = (g.K + BK - 1) / BK;
+    const int64_t kb_per_z = g.kchunk / BK;
+
+    if (warp == 0) {
+        // ================= TMA producer =================
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            for (int64_t t = blockIdx.x; t < total; t += gridDim.x) {
+                const int z = (int)(t / tiles_mn);
+                const int64_t mn = t - (int64_t)z * tiles_mn;
+                const int m0 = (int)(mn % g.mt) * BM, n0 = (int)(mn / g.mt) * BN;
+                const int64_t kb0 = z * kb_per_z, kb1 = min(kb_all, kb0 + kb_per_z);
+                for (int64_t kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(bar_empty(s), ph ^ 1u);
+                    mbar_expect_tx(bar_full(s), A_TILE_BYTES + C::B_TILE_BYTES);
+                    const int k0 = (int)(kb * BK);
+                    if (A_MN) {
+#pragma unroll
+                        for (int j = 0; j < BM / 32; ++j) tma_load_2d(a_hi(s) + j * 4096, &mapA, bar_full(s), m0 + 32 * j, k0);
+                    } else {
+                        tma_load_2d(a_hi(s), &mapA, bar_full(s), k0, m0);
+                    }
+                    if (B_MN) {
+#pragma unroll
+                        for (int j = 0; j < BN / 32; ++j) tma_load_2d(b_hi(s) + j * 4096, &mapB, bar_full(s), n0 + 32 * j, k0);
+                    } else {
+                        tma_load_2d(b_hi(s), &mapB, bar_full(s), k0, n0);
+                    }
+                    if (++s == C::STAGES) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            // instruction descriptor (cute::UMMA::InstrDescriptor): D=f32 [4,6), A=tf32 [7,10), B=tf32 [10,13),
+            // a_major [15], b_major [16], N>>3 [17,23), M>>4 [24,29)
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                                   ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            // K-major (SWIZZLE_128B): 8-row groups 1024 B apart (SBO), k step = 32 B inside the swizzle row.
+            // MN-major (SWIZZLE_128B_BASE32B, atom = 4 k-rows x 128 B): 32-column chunks 4096 B apart (LBO),
+            // 4-k-row groups 512 B apart (SBO), k step of 8 rows = 1024 B.
+            constexpr uint32_t A_LBO = A_MN ? 4096 : 16, A_SBO = A_MN ? 512 : 1024, A_STEP = A_MN ? 1024 : 32, A_LAY = A_MN ? 1 : 2;
+            constexpr uint32_t B_LBO = B_MN ? 4096 : 16, B_SBO = B_MN ? 512 : 1024, B_STEP = B_MN ? 1024 : 32, B_LAY = B_MN ? 1 : 2;
+            int s = 0, a = 0;
+            uint32_t ph = 0, aph = 0;
+            for (int64_t t = blockIdx.x; t < total; t += gridDim.x) {
+                const int z = (int)(t / tiles_mn);
+                const int64_t kb0 = z * kb_per_z, kb1 = min(kb_all, kb0 + kb_per_z);
+                for (int64_t kg = kb0; kg < kb1; kg += g.kgroup) {
+                    const int64_t kge = min(kb1, kg + g.kgroup);
+                    mbar_wait(bar_tempty(a), aph ^ 1u);
+                    tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
+                    for (int64_t kb = kg; kb < kge; ++kb) {
+                        mbar_wait(bar_conv(s), ph);
+                        tc_fence_after();
+                        const uint64_t ah = smem_desc(a_hi(s), A_LBO, A_SBO, A_LAY), al = smem_desc(a_lo(s), A_LBO, A_SBO, A_LAY);
+                        const uint64_t bh = smem_desc(b_hi(s), B_LBO, B_SBO, B_LAY), bl = smem_desc(b_lo(s), B_LBO, B_SBO, B_LAY);
+#pragma unroll
+                        for (int k = 0; k < BK / UK; ++k) {
+                            const uint64_t ao = (uint64_t)((k * A_STEP) >> 4), bo = (uint64_t)((k * B_STEP) >> 4);
+                            tc_mma_tf32(d_tmem, al + ao, bh + bo, idesc, (kb > kg || k > 0) ? 1u : 0u);
+                            tc_mma_tf32(d_tmem, ah + ao, bl + bo, idesc, 1u);
+                            tc_mma_tf32(d_tmem, ah + ao, bh + bo, idesc, 1u);
+                        }
+                        tc_commit(bar_empty(s));  // smem stage may be refilled once these MMAs have read it
+                        if (++s == C::STAGES) { s = 0; ph ^= 1u; }
+                    }
+                    tc_commit(bar_tfull(a));      // accumulator chain complete
+                    if (++a == 2) { a = 0; aph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp < EPI_WARP0) {
+        // ================= splitters: raw -> hi (in place), lo =================
+        const int tid = threadIdx.x - SPLIT_WARP0 * 32;  // 0..127
+        int s = 0;
+        uint32_t ph = 0;
+        for (int64_t t = blockIdx.x; t < total; t += gridDim.x) {
+            const int z = (int)(t / tiles_mn);
+            const int64_t kb0 = z * kb_per_z, kb1 = min(kb_all, kb0 + kb_per_z);
+            for (int64_t kb = kb0; kb < kb1; ++kb) {
+                mbar_wait(bar_full(s), ph);
+                float4 *hi = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES);
+                float4 *lo = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + A_TILE_BYTES);
+                auto split4 = [](float4 *ph4, float4 *pl4) {
+                    float4 x = *ph4, h, l;
+                    uint32_t u;
+#define MGGCN_SPLIT(c)                                                                   \
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.c));                                \
+    h.c = __uint_as_float(u);                                                            \
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.c - h.c));                          \
+    l.c = __uint_as_float(u);
+                    MGGCN_SPLIT(x) MGGCN_SPLIT(y) MGGCN_SPLIT(z) MGGCN_SPLIT(w)
+#undef MGGCN_SPLIT
+                    *ph4 = h;
+                    *pl4 = l;
+                };
+#pragma unroll
+                for (int i = 0; i < (int)(A_TILE_BYTES / 16 / 128); ++i) split4(hi + tid + 128 * i, lo + tid + 128 * i);
+                float4 *bhi = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES);
+                float4 *blo = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES + C::B_TILE_BYTES);
+#pragma unroll
+                for (int i = 0; i < (int)(C::B_TILE_BYTES / 16 / 128); ++i) split4(bhi + tid + 128 * i, blo + tid + 128 * i);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> tensor-core reads
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_conv(s));
+                if (++s == C::STAGES) { s = 0; ph ^= 1u; }
+            }
+        }
+    } else {
+        // ================= accumulate + epilogue =================
+        // 8 warps: warp w may read TMEM lanes 32*(w%4)..+31 only, so two warps share each lane quarter
+        // and take half of the tile's columns each.
+        constexpr int CW = BN / 2;           // columns per warp
+        const int q = warp & 3;              // TMEM lane quarter (= 32 tile rows)
+        const int ew = warp - EPI_WARP0;     // staging slot 0..7
+        const int half = ew >> 2;
+        float *my_stg = stg + ew * 32 * STG_LD;
+        int a = 0;
+        uint32_t aph = 0;
+        for (int64_t t = blockIdx.x; t < total; t += gridDim.x) {
+            const int z = (int)(t / tiles_mn);
+            const int64_t mn = t - (int64_t)z * tiles_mn;
+            const int64_t m0 = (int64_t)(mn % g.mt) * BM, n0 = (int64_t)(mn / g.mt) * BN + half * CW;
+            const int64_t kb0 = z * kb_per_z, kb1 = min(kb_all, kb0 + kb_per_z);
+            float acc[CW];
+#pragma unroll
+            for (int i = 0; i < CW; ++i) acc[i] = 0.f;
+            for (int64_t kg = kb0; kg < kb1; kg += g.kgroup) {
+                mbar_wait(bar_tfull(a), aph);
+                tc_fence_after();
+#pragma unroll
+                for (int c = 0; c < CW / 32; ++c) {
+                    float v[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN + half * CW + c * 32), v);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) acc[c * 32 + j] += v[j];
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_tempty(a));
+                if (++a == 2) { a = 0; aph ^= 1u; }
+            }
+            // store: rows m0 + 32q .. +31, 16 columns at a time through the staging slot.  The slot is
+            // written thread-per-row (what tcgen05.ld delivers) and read back 8 rows x 4 float4 per
+            // instruction: every global access of the warp is made of whole 64-byte row pieces and one lane
+            // finishes 4 elements per instruction.  Operands of the epilogue (the activation input of the
+            // LeakyReLU gradient, beta*C) are loaded for all row groups of a chunk before its first store.
+            const bool split = g.nz > 1;
+            float *out = split ? g.part + (int64_t)z * g.M * g.N : g.C;
+            const int64_t ldo = split ? g.N : g.ldc;
+            const bool use_aux = !split && g.epi.kind == MGGCN_EPI_LEAKY_RELU_BWD;
+            const bool use_old = !split && g.beta != 0.f;
+            const bool vec_ok = (reinterpret_cast<uintptr_t>(out) & 15) == 0 && ldo % 4 == 0 &&
+                                (split || (!g.epi.keep_mask &&
+                                           (!use_aux || ((reinterpret_cast<uintptr_t>(g.epi.aux) & 15) == 0 && g.epi.ld_aux % 4 == 0))));
+            const int r_in = lane >> 2, c4 = (lane & 3) * 4;
+            const int64_t row0 = m0 + q * 32 + r_in;
+#pragma unroll
+            for (int c = 0; c < CW / 16; ++c) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    *reinterpret_cast<float4 *>(my_stg + lane * STG_LD + 4 * j) =
+                        make_float4(acc[c * 16 + 4 * j], acc[c * 16 + 4 * j + 1], acc[c * 16 + 4 * j + 2], acc[c * 16 + 4 * j + 3]);
+                __syncwarp();
+                const int64_t col = n0 + c * 16 + c4;
+                if (vec_ok && col + 3 < g.N) {
+                    float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (!split && g.epi.bias) bias = make_float4(__ldg(g.epi.bias + col), __ldg(g.epi.bias + col + 1),
+                                                                 __ldg(g.epi.bias + col + 2), __ldg(g.epi.bias + col + 3));
+                    float4 zz[4], old[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) zz[i] = old[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (use_aux) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (row0 + 8 * i < g.M)
+                                zz[i] = __ldg(reinterpret_cast<const float4 *>(g.epi.aux + (row0 + 8 * i) * g.epi.ld_aux + col));
+                    }
+                    if (use_old) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (row0 + 8 * i < g.M) old[i] = *reinterpret_cast<const float4 *>(out + (row0 + 8 * i) * ldo + col);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int64_t row = row0 + 8 * i;
+                        if (row >= g.M) break;
+                        float4 x4 = *reinterpret_cast<const float4 *>(my_stg + (8 * i + r_in) * STG_LD + c4);
+                        if (!split) {
+                            float x[4] = {x4.x, x4.y, x4.z, x4.w};
+                            const float o[4] = {old[i].x, old[i].y, old[i].z, old[i].w};
+                            const float zv[4] = {zz[i].x, zz[i].y, zz[i].z, zz[i].w};
+                            const float bv[4] = {bias.x, bias.y, bias.z, bias.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                float y = x[e] * g.alpha;
+                                if (use_old) y += g.beta * o[e];
+                                y += bv[e];
+                                if (g.epi.kind == MGGCN_EPI_LEAKY_RELU) {
+                                    const float ay = g.epi.slope * y;
+                                    y = y > ay ? y : ay;
+                                } else if (use_aux) {
+                                    y = zv[e] > 0.f ? y : g.epi.slope * y;
+                                }
+                                x[e] = y;
+                            }
+                            x4 = make_float4(x[0], x[1], x[2], x[3]);
+                        }
+                        *reinterpret_cast<float4 *>(out + row * ldo + col) = x4;
+                    }
+                } else if (col < g.N) {
+                    for (int i = 0; i < 4; ++i) {
+                        const int64_t row = row0 + 8 * i;
+                        if (row >= g.M) break;
+                        for (int e = 0; e < 4 && col + e < g.N; ++e) {
+                            float x = my_stg[(8 * i + r_in) * STG_LD + c4 + e];
+                            float *cp = out + row * ldo + col + e;
+                            if (!split) {
+                                x *= g.alpha;
+                                if (g.beta != 0.f) x += g.beta * *cp;
+                                x = epi_apply(x, g.epi, row, col + e, g.epi.bias ? __ldg(g.epi.bias + col + e) : 0.f);
+                            }
+                            *cp = x;
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
+                     : "memory");
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+encode_tiled_fn g_encode = nullptr;
+int g_sm_count = 0;
+bool g_tc_usable = false;
+std::once_flag g_once;
+
+void tc_init() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return;
+    int major = 0;
+    cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn) {
+        cudaGetLastError();
+        return;
+    }
+    g_encode = reinterpret_cast<encode_tiled_fn>(fn);
+    g_tc_usable = major == 10 && g_sm_count > 0;
+}
+
+// 2-D fp32 tensor map over a row-major array: `inner` contiguous elements, `outer` rows of `ld` elements.
+// mn_major: the operand's M/N index is the contiguous one -> 32-byte-atom 128-byte swizzle (see smem_desc)
+int make_map(CUtensorMap *m, const float *p, int64_t inner, int64_t outer, int64_t ld, uint32_t box_inner,
+             uint32_t box_outer, bool mn_major) {
+    cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(p), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(MGGCN_E_INVALID, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return MGGCN_OK;
+}
+
+struct split_plan {
+    int nz;
+    int64_t kchunk;
+};
+split_plan plan_split(int ta, int64_t M, int64_t N, int64_t K, int bn) {
+    const int64_t kb_all = (K + BK - 1) / BK;
+    split_plan p{1, std::max<int64_t>(kb_all, 1) * BK};
+    if (!ta || K < 4096) return p;
+    const int64_t tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+    const int sms = g_sm_count > 0 ? g_sm_count : 148;
+    int64_t nz = std::max<int64_t>(1, sms / tiles);
+    nz = std::min<int64_t>(nz, std::max<int64_t>(1, kb_all / 8));  // at least 8 k-blocks per slice
+    if (nz <= 1) return p;
+    const int64_t kb_per = (kb_all + nz - 1) / nz;
+    p.kchunk = kb_per * BK;
+    p.nz = (int)((kb_all + kb_per - 1) / kb_per);
+    return p;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+int launch(cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const tc_args &g) {
+    using C = cfg<BN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MGGCN_CUDA_TRY(cudaFuncSetAttribute(gemm_tc_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)C::SMEM_BYTES));
+        attr_set = true;
+    }
+    const int64_t total = (int64_t)g.mt * g.nt * g.nz;
+    const unsigned grid = (unsigned)std::min<int64_t>(total, g_sm_count);
+    gemm_tc_kernel<BN, A_MN, B_MN><<<grid, NTHREADS, C::SMEM_BYTES, st>>>(ma, mb, g);
+    MGGCN_LAUNCH_CHECK();
+    return MGGCN_OK;
+}
+
+}  // namespace
+
+namespace mggcn {
+
+int launch_splitk_reduce(cudaStream_t st, const float *part, int nz, int64_t M, int64_t N, float *C, int64_t ldc,
+                         float alpha, float beta, const mggcn_epilogue &epi);
+
+bool gemm_tc_eligible(int64_t M, int64_t N, int64_t K, const float *A, int64_t lda, const float *B, int64_t ldb) {
+    std::call_once(g_once, tc_init);
+    if (!g_tc_usable || !g_gemm_tc) return false;
+    if (M < 1 || N < 1 || K < 1 || N > 128 * 65535ll) return false;
+    if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) || lda % 4 || ldb % 4) return false;
+    if (M * N * K < (1ll << 18)) return false;  // tiny products: the SIMT kernel has no setup cost
+    return true;
+}
+
+size_t gemm_tc_workspace_bytes(int ta, int64_t M, int64_t N, int64_t K) {
+    std::call_once(g_once, tc_init);
+    const split_plan p = plan_split(ta, M, N, K, N <= 64 ? 64 : 128);
+    return p.nz > 1 ? (size_t)p.nz * (size_t)M * (size_t)N * sizeof(float) : 0;
+}
+
+int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, float alpha, const float *A, int64_t lda,
+            const float *B, int64_t ldb, float beta, float *C, int64_t ldc, const mggcn_epilogue &epi, void *ws,
+            size_t ws_bytes) {
+    const int bn = N <= 64 ? 64 : 128;
+    split_plan sp = plan_split(ta, M, N, K, bn);
+    if (sp.nz > 1 && (!ws || ws_bytes < (size_t)sp.nz * M * N * sizeof(float))) {
+        sp.nz = 1;
+        sp.kchunk = (K + BK - 1) / BK * BK;
+    }
+    CUtensorMap ma, mb;
+    // A: ta -> stored K x M (inner = M), boxes of 32 m x 32 k; else stored M x K (inner = K), box 32 k x 128 m
+    if (ta) { int rc = make_map(&ma, A, M, K, lda, 32, BK, true); if (rc) return rc; }
+    else { int rc = make_map(&ma, A, K, M, lda, BK, BM, false); if (rc) return rc; }
+    // B: tb -> stored N x K (inner = K), box 32 k x BN n; else stored K x N (inner = N), boxes of 32 n x 32 k
+    if (tb) { int rc = make_map(&mb, B, K, N, ldb, BK, (uint32_t)bn, false); if (rc) return rc; }
+    else { int rc = make_map(&mb, B, N, K, ldb, 32, BK, true); if (rc) return rc; }
+    tc_args g{};
+    g.M = M; g.N = N; g.K = K;
+    g.C = C; g.ldc = ldc;
+    g.part = static_cast<float *>(ws);
+    g.nz = sp.nz;
+    g.kchunk = sp.kchunk;
+    g.mt = (int)((M + BM - 1) / BM);
+    g.nt = (int)((N + bn - 1) / bn);
+    g.kgroup = std::max(1, g_gemm_kgroup);
+    g.alpha = alpha; g.beta = beta;
+    g.epi = epi;
+    int rc;
+    if (bn == 64) {
+        if (ta && !tb) rc = launch<64, true, true>(st, ma, mb, g);
+        else if (ta && tb) rc = launch<64, true, false>(st, ma, mb, g);
+        else if (!ta && tb) rc = launch<64, false, false>(st, ma, mb, g);
+        else rc = launch<64, false, true>(st, ma, mb, g);
+    } else {
+        if (ta && !tb) rc = launch<128, true, true>(st, ma, mb, g);
+        else if (ta && tb) rc = launch<128, true, false>(st, ma, mb, g);
+        else if (!ta && tb) rc = launch<128, false, false>(st, ma, mb, g);
+        else rc = launch<128, false, true>(st, ma, mb, g);
+    }
+    if (rc) return rc;
+    if (sp.nz > 1) return launch_splitk_reduce(st, g.part, sp.nz, M, N, C, ldc, alpha, beta, epi);
+    return MGGCN_OK;
+}
+
+}  // namespace mggcn

@@ -29,6 +29,10 @@
 
 using namespace mggcn;
 
+namespace mggcn {
+extern int g_gemm_tc, g_gemm_kgroup;  // gemm_tc.cu
+}
+
 namespace {
 
 struct alignas(16) spmm_item {
@@ -563,6 +567,8 @@ int mggcn_tune(const char *key, int value) {
     else if (!strcmp(key, "threads")) slot = &g_threads;
     else if (!strcmp(key, "policy")) slot = &g_policy;
     else if (!strcmp(key, "split")) slot = &g_split;
+    else if (!strcmp(key, "gemm_tc")) slot = &mggcn::g_gemm_tc;
+    else if (!strcmp(key, "gemm_kgroup")) slot = &mggcn::g_gemm_kgroup;
     if (!slot) return fail(MGGCN_E_INVALID, "unknown tuning key %s", key);
     const int old = *slot;
     if (slot == &g_threads && (value < 32 || value > 256 || value % 32)) return fail(MGGCN_E_INVALID, "threads must be 32..256");

@@ -60,6 +60,12 @@ def main():
         return float(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64)).max() / max(np.abs(b).max(), 1e-30))
 
     for epoch in range(args.epochs):
+        if not args.graph and epoch > 0:
+            # per-layer bars are for identical parameters (Adam amplifies fp32 rounding differences over
+            # epochs; the unsynchronised trajectory is what the --graph variant checks on the loss)
+            for l in range(L):
+                ref.set_tensor(f"W{l}", eng.get(f"W{l}"))
+                ref.set_tensor(f"b{l}", eng.get(f"b{l}"))
         if args.graph:
             eng.epoch()
             ls, cs = eng.loss()

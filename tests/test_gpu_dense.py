@@ -49,6 +49,27 @@ def test_gemm_epilogues_alpha_beta_strided(mg, cuda):
         assert np.array_equal(got[:, N:], C0[:, N:])
 
 
+@pytest.mark.parametrize("tb,M,N,K", [(1, 1000, 128, 128), (0, 777, 128, 608), (1, 515, 64, 41)])
+def test_gemm_vector_epilogue_paths(mg, cuda, tb, M, N, K):
+    """The float4 epilogue of the tensor-core kernel: bias + LeakyReLU, LeakyReLU gradient with aux, beta*C."""
+    torch = cuda
+    rng = np.random.default_rng(7)
+    A = rng.standard_normal((M, K)).astype(np.float32)
+    B = rng.standard_normal((N, K) if tb else (K, N)).astype(np.float32)
+    C0 = rng.standard_normal((M, N)).astype(np.float32)
+    Z = rng.standard_normal((M, N)).astype(np.float32)
+    bias = rng.standard_normal(N).astype(np.float32)
+    prod = A.astype(np.float64) @ (B.T if tb else B).astype(np.float64)
+    tol = 1e-5 * float((np.abs(A).astype(np.float64) @ np.abs(B.T if tb else B)).max())
+    At, Bt, Zt, bt = (torch.from_numpy(x).cuda() for x in (A, B, Z, bias))
+    for epi, beta, want in ((mg.make_epilogue(mg.EPI_LEAKY_RELU, 0.01, bias=bt), 0.0, np.where(prod + bias > 0, prod + bias, 0.01 * (prod + bias))),
+                            (mg.make_epilogue(mg.EPI_LEAKY_RELU_BWD, 0.01, aux=Zt), 0.0, np.where(Z > 0, prod, 0.01 * prod)),
+                            (None, 1.0, prod + C0)):
+        Ct = torch.from_numpy(C0.copy()).cuda()
+        mg.gemm(At, Bt, Ct, tb=bool(tb), beta=beta, epi=epi)
+        np.testing.assert_allclose(Ct.cpu().numpy(), want, rtol=0, atol=tol)
+
+
 def test_colsum_and_elementwise(mg, orc, cuda):
     torch = cuda
     rng = np.random.default_rng(2)

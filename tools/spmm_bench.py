@@ -35,6 +35,7 @@ def main():
     ap.add_argument("--blocks", type=int, default=1, help="P: time the diagonal block (0,0) of a P x P split")
     ap.add_argument("--cusparse", action="store_true")
     ap.add_argument("--splits", type=int, nargs="*", default=[])
+    ap.add_argument("--slices", type=int, nargs="*", default=[], help="feature-slice counts: k launches over F/k-wide column windows")
     ap.add_argument("--unroll", type=int, default=4)
     ap.add_argument("--threads", type=int, default=64)
     args = ap.parse_args()
@@ -77,6 +78,16 @@ def main():
             pl = mg.SpmmPlan(AT.rowptr.astype(np.uint32), split_nnz=sp)
             med, mn = timeit(lambda: mg.spmm(rpt, cit, vat, B, Cm, cols=m, F=F, plan=pl))
             report("ours-split", med, mn, split=sp)
+        for k in args.slices:
+            if F % (4 * k):
+                continue
+            w = F // k
+
+            def sliced():
+                for i in range(k):
+                    mg.spmm(rpt, cit, vat, B[:, i * w:(i + 1) * w], Cm[:, i * w:(i + 1) * w], cols=m, F=w, plan=plan)
+            med, mn = timeit(sliced)
+            report("ours-sliced", med, mn, slices=k)
         if args.cusparse:
             S = torch.sparse_csr_tensor(rpt.to(torch.int32), cit, vat, size=(n, m))
             Bc = B[:, :F].contiguous()
