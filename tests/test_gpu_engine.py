@@ -46,7 +46,18 @@ def test_layers_grads_and_loss_curve(mg, orc, cuda, shape, hidden, exact):
         assert abs(cs / A.n - racc) <= 2.0 / A.n + 1e-6
         if epoch in (0, 9):
             for l in range(L - 1):  # the last layer's buffer holds the loss gradient by now
-                assert rel(eng.get(f"H{l}"), ref.tensor(f"H{l}")) <= 1e-5, (epoch, l)
+                he, hr = eng.get(f"H{l}"), ref.tensor(f"H{l}")
+                assert rel(he, hr) <= 1e-5, (epoch, l)
+                # LeakyReLU's derivative jumps at 0: a pre-activation whose magnitude is below the rounding
+                # noise of the sums (measured on B200: one element of 262,144 with |Z| = 1e-9 at epoch 9) may
+                # land on either side, and its gradient then differs by the factor 1/slope.  Such elements must
+                # be inside the 1e-5 band above; the oracle is put on the engine's side of the kink so that the
+                # gradient comparison below tests the arithmetic and not the coin toss.
+                flip = np.nonzero((he > 0) != (hr > 0))[0]
+                assert len(flip) <= 4, (epoch, l, len(flip))
+                if len(flip):
+                    hr[flip] = he[flip]
+                    ref.set_tensor(f"H{l}", hr)
         eng.backward(); ref.backward()
         if epoch in (0, 9):
             # A weight gradient is a sum over all vertices of products that largely cancel once training has
