@@ -306,6 +306,12 @@ MGGCN_API int mggcn_engine_adam_update(mggcn_engine_t *e, float lr, float beta1,
 /* One whole epoch (forward, loss, backward, Adam) enqueued back to back; no host sync. */
 MGGCN_API int mggcn_engine_epoch(mggcn_engine_t *e, float lr, float beta1, float beta2, float wd,
                                  float eps);
+/* Captures and instantiates the epoch graph without launching it (no-op when use_graph == 0).
+ * A process that drives several engines prepares ALL of them before it launches any: graph
+ * instantiation allocates device memory, which waits for peer-mapped GPUs to go idle, while a launched
+ * engine spins in its first stage barrier until its peers are launched. */
+MGGCN_API int mggcn_engine_prepare(mggcn_engine_t *e, float lr, float beta1, float beta2, float wd,
+                                   float eps);
 /* Blocks until the rank's streams are idle, then returns this rank's partial sums
  * (sum |log p_y|, number correct) of the last train_forward. */
 MGGCN_API int mggcn_engine_loss(mggcn_engine_t *e, double *loss_sum, double *correct);

@@ -109,6 +109,7 @@ _SIGS = {
     "mggcn_engine_backward": (C.c_int, [_vp]),
     "mggcn_engine_adam_update": (C.c_int, [_vp, _f32, _f32, _f32, _f32, _f32]),
     "mggcn_engine_epoch": (C.c_int, [_vp, _f32, _f32, _f32, _f32, _f32]),
+    "mggcn_engine_prepare": (C.c_int, [_vp, _f32, _f32, _f32, _f32, _f32]),
     "mggcn_engine_loss": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "mggcn_engine_sync": (C.c_int, [_vp]),
     "mggcn_engine_stream": (_vp, [_vp, _i32]),

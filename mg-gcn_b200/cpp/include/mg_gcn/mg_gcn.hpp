@@ -1,0 +1,111 @@
+// mg_gcn.hpp -- conventions shared by the C++ surface: error policy, buffer ownership, types.
+//
+// Mirrors the role of the reference's src/mg_gcn.hpp:1-132 (CHECK_* macros that print and exit,
+// cuda_ptr<T> = shared_ptr<T[]> with a CUDA deleter, cuda_malloc / cuda_malloc_managed).  The
+// surface is header-only C++17 over the C-ABI of include/mggcn.h; it needs the CUDA runtime
+// headers only for allocation, copies, streams and events -- every kernel lives behind the ABI.
+#pragma once
+
+#include <cuda_runtime_api.h>
+
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+
+#include "mggcn.h"
+
+namespace mg_gcn {
+
+// Fail-fast policy of the reference's C++ surface (src/mg_gcn.hpp:31-68): print and exit.
+// The C-ABI below never exits; it hands back a code and a message.
+#define CHECK_CUDA(call)                                                                           \
+    do {                                                                                           \
+        cudaError_t status__ = (call);                                                             \
+        if (status__ != cudaSuccess) {                                                             \
+            std::printf("CUDA failure at %s:%d: %s (%d)\n", __FILE__, __LINE__,                    \
+                        cudaGetErrorString(status__), (int)status__);                              \
+            std::exit(EXIT_FAILURE);                                                               \
+        }                                                                                          \
+    } while (0)
+
+#define CHECK_MGGCN(call)                                                                          \
+    do {                                                                                           \
+        int status__ = (call);                                                                     \
+        if (status__ != MGGCN_OK) {                                                                \
+            std::printf("mggcn failure at %s:%d: %s (%d)\n", __FILE__, __LINE__,                   \
+                        mggcn_last_error(), status__);                                             \
+            std::exit(EXIT_FAILURE);                                                               \
+        }                                                                                          \
+    } while (0)
+
+// bad files / bad arguments are exceptions, caught in main (src/matrix.hpp:33-37, src/main.cpp:198-209)
+class matrix_error : public std::runtime_error {
+   public:
+    template <typename T>
+    explicit matrix_error(T t) : std::runtime_error(t) {}
+};
+
+template <typename T>
+using cuda_ptr = std::shared_ptr<T[]>;
+
+// True when a CUDA device can be used by this process.  Host-only tools (file conversion,
+// pre-processing, the generator) run without one; every compute entry point needs one.
+inline bool have_device() {
+    static const bool ok = [] {
+        int n = 0;
+        const cudaError_t e = cudaGetDeviceCount(&n);
+        if (e != cudaSuccess) cudaGetLastError();
+        return e == cudaSuccess && n > 0;
+    }();
+    return ok;
+}
+
+// Host-indexable buffers, like the reference's cudaMallocManaged containers (src/mg_gcn.hpp:74-82):
+// callers index matrices on the host (operator[]) and hand the same pointer to kernels.  Without a
+// device the allocation is plain host memory so that the host half of the surface still works.
+template <typename T>
+cuda_ptr<T> cuda_malloc_managed(std::size_t count) {
+    if (count == 0) count = 1;
+    T *p = nullptr;
+    if (have_device()) {
+        CHECK_CUDA(cudaMallocManaged(reinterpret_cast<void **>(&p), count * sizeof(T)));
+        return cuda_ptr<T>(p, [](T *q) { cudaFree(q); });
+    }
+    p = static_cast<T *>(std::malloc(count * sizeof(T)));
+    if (!p) throw std::bad_alloc();
+    return cuda_ptr<T>(p, [](T *q) { std::free(q); });
+}
+
+// Device-only buffers (src/mg_gcn.hpp:84-90).
+template <typename T>
+cuda_ptr<T> cuda_malloc(std::size_t count) {
+    if (count == 0) count = 1;
+    T *p = nullptr;
+    CHECK_CUDA(cudaMalloc(reinterpret_cast<void **>(&p), count * sizeof(T)));
+    return cuda_ptr<T>(p, [](T *q) { cudaFree(q); });
+}
+
+// Moves a managed range next to the GPU that is about to read it, so the first epoch does not pay
+// page faults (the reference never prefetches or advises).
+inline void prefetch_to_device(const void *p, std::size_t bytes, int device, cudaStream_t st = nullptr) {
+    if (!have_device() || !p || !bytes) return;
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess || a.type != cudaMemoryTypeManaged) {
+        cudaGetLastError();
+        return;
+    }
+#if CUDART_VERSION >= 13000
+    cudaMemLocation loc{cudaMemLocationTypeDevice, device};
+    cudaMemPrefetchAsync(p, bytes, loc, 0, st);
+#else
+    cudaMemPrefetchAsync(p, bytes, device, st);
+#endif
+    cudaGetLastError();
+}
+
+}  // namespace mg_gcn

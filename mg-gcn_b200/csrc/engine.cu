@@ -85,6 +85,21 @@ int nccl_load() {
     } while (0)
 
 inline int64_t up4(int64_t x) { return (x + 3) / 4 * 4; }
+
+// MGGCN_TRACE=1: host-side time stamps of the enqueue path (finds calls that block the launching thread)
+inline bool trace_on() {
+    static const bool on = getenv("MGGCN_TRACE") != nullptr;
+    return on;
+}
+inline double trace_ms() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
+#define TRACE(rank, label)                                                               \
+    do {                                                                                 \
+        if (trace_on()) fprintf(stderr, "[trace r%d] %.3f %s\n", (rank), trace_ms(), (label)); \
+    } while (0)
 inline size_t up256(size_t x) { return (x + 255) / 256 * 256; }
 
 // ---------------------------------------------------------------------------------------------
@@ -99,7 +114,8 @@ struct peer_table {
 // Flag barrier over peer-mapped memory.  Slot k has its own monotonically increasing ticket, kept
 // on the device so that a captured graph can be replayed.  Every rank runs the same sequence of
 // barriers, so the tickets agree.  A timeout (about 10 s of SM clock) raises *err instead of hanging.
-__global__ void xbarrier_kernel(peer_table pt, uint32_t *tickets, int slot, int rank, int P, int *err) {
+__global__ void xbarrier_kernel(peer_table pt, uint32_t *tickets, int slot, int rank, int P, int *err,
+                                long long timeout_cycles) {
     __shared__ uint32_t ticket;
     if (threadIdx.x == 0) ticket = ++tickets[slot];
     __syncthreads();
@@ -112,7 +128,7 @@ __global__ void xbarrier_kernel(peer_table pt, uint32_t *tickets, int slot, int 
         volatile uint32_t *src = pt.flags[rank] + slot * kMaxRanks + t;
         const long long t0 = clock64();
         while ((int32_t)(*src - ticket) < 0) {
-            if (clock64() - t0 > 20000000000ll) {
+            if (clock64() - t0 > timeout_cycles) {
                 *err = 1;
                 break;
             }
@@ -283,7 +299,13 @@ int xbarrier(eng *e, cudaStream_t st) {
     if (slot >= kBarrierSlots) return fail(MGGCN_E_STATE, "too many barriers in one epoch");
     peer_table pt{};
     for (int r = 0; r < e->P; ++r) pt.flags[r] = reinterpret_cast<uint32_t *>(e->peer_arena[r]);
-    xbarrier_kernel<<<1, 32, 0, st>>>(pt, e->tickets, slot, e->rank, e->P, e->dev_err);
+    // about 10 s of SM clock by default; MGGCN_BARRIER_TIMEOUT_MS shortens it for tests
+    static const long long cycles = [] {
+        const char *v = getenv("MGGCN_BARRIER_TIMEOUT_MS");
+        const long long ms = v && atoll(v) > 0 ? atoll(v) : 10000;
+        return ms * 2000000ll;
+    }();
+    xbarrier_kernel<<<1, 32, 0, st>>>(pt, e->tickets, slot, e->rank, e->P, e->dev_err, cycles);
     MGGCN_LAUNCH_CHECK();
     return MGGCN_OK;
 }
@@ -306,7 +328,9 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
     const size_t off = (size_t)(reinterpret_cast<const char *>(B) - e->arena);
     MGGCN_CUDA_TRY(cudaEventRecord(e->ev_ready, e->sc));
     if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sm, e->ev_ready, 0));
+    TRACE(e->rank, "dist_spmm: events recorded");
     if (e->p2p) TRY(xbarrier(e, e->sm));  // every rank's B is complete
+    TRACE(e->rank, "dist_spmm: barrier launched");
     int t_all, t_x, t_s;
     TRY(timer_begin(e, tname + "matmul-spmm", e->sc, &t_all));
     for (int s = 0; s < P; ++s) {
@@ -322,6 +346,7 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
                 MGGCN_CUDA_TRY(cudaMemcpyAsync(e->stage[s & 1], e->peer_arena[blk] + off, count * sizeof(float),
                                                cudaMemcpyDeviceToDevice, e->sm));
                 src = e->stage[s & 1];
+                TRACE(e->rank, "dist_spmm: peer copy enqueued");
             } else if (blk == e->rank) {
                 NCCL_TRY(g_nccl.Broadcast(B, const_cast<float *>(B), count, ncclFloat, blk, e->comm, e->sm));
             } else {
@@ -339,6 +364,7 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
         TRY(mggcn_spmm_csr_f32_i32(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, src, ld, C, ld, (int)F, 1.f,
                                    s == 0 ? 0.f : 1.f, last ? epi : nullptr, a.plan, e->ws_spmm));
         TRY(timer_end(e, e->sc, t_s));
+        TRACE(e->rank, "dist_spmm: stage spmm launched");
         if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaEventRecord(e->ev_spmm[s], e->sc));
     }
     TRY(timer_end(e, e->sc, t_all));
@@ -360,6 +386,7 @@ int gemm(eng *e, int ta, int tb, int64_t M, int64_t N, int64_t K, const float *A
 
 int forward(eng *e) {
     int tg;
+    TRACE(e->rank, "forward: begin");
     const float *H = e->X;
     int64_t ldH = e->ldX;
     for (int l = 0; l < e->L; ++l) {
@@ -393,6 +420,7 @@ int forward(eng *e) {
     TRY(mggcn_softmax_xent_f32(e->sc, last.Z, up4(last.out), e->n, (int)last.out, e->Y, 1.f / (float)e->N,
                                e->loss_out, e->ws_loss, e->ws_loss_bytes));
     TRY(timer_end(e, e->sc, tg));
+    TRACE(e->rank, "forward: end");
     return MGGCN_OK;
 }
 
@@ -677,7 +705,7 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
             wo += (size_t)(y.in * y.out);
             bo += (size_t)y.out;
         }
-        E_CUDA(cudaMemcpy(e->params, host.data(), e->n_params * 4, cudaMemcpyHostToDevice));
+        E_CUDA(cudaMemcpy(e->params, host.data(), e->n_params * 4, cudaMemcpyDefault));
     }
 
     if (e->P > 1 && !e->p2p) {
@@ -717,11 +745,11 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
         std::vector<uint32_t> rp32((size_t)a.rows + 1);
         for (int64_t r = 0; r <= a.rows; ++r) rp32[(size_t)r] = (uint32_t)rp[r];
         MGGCN_CUDA_TRY(cudaMalloc(&a.rowptr, rp32.size() * 4));
-        MGGCN_CUDA_TRY(cudaMemcpy(a.rowptr, rp32.data(), rp32.size() * 4, cudaMemcpyHostToDevice));
+        MGGCN_CUDA_TRY(cudaMemcpy(a.rowptr, rp32.data(), rp32.size() * 4, cudaMemcpyDefault));
         MGGCN_CUDA_TRY(cudaMalloc(&a.colidx, std::max<size_t>((size_t)a.nnz, 1) * 4));
         MGGCN_CUDA_TRY(cudaMalloc(&a.vals, std::max<size_t>((size_t)a.nnz, 1) * 4));
-        MGGCN_CUDA_TRY(cudaMemcpy(a.colidx, blk_colidx[j], (size_t)a.nnz * 4, cudaMemcpyHostToDevice));
-        MGGCN_CUDA_TRY(cudaMemcpy(a.vals, blk_vals[j], (size_t)a.nnz * 4, cudaMemcpyHostToDevice));
+        MGGCN_CUDA_TRY(cudaMemcpy(a.colidx, blk_colidx[j], (size_t)a.nnz * 4, cudaMemcpyDefault));
+        MGGCN_CUDA_TRY(cudaMemcpy(a.vals, blk_vals[j], (size_t)a.nnz * 4, cudaMemcpyDefault));
         TRY(mggcn_spmm_plan_create_i32(a.rows, rp32.data(), 0, &a.plan));
         ws = std::max(ws, mggcn_spmm_plan_workspace_bytes(a.plan, (int)e->maxw));
     }
@@ -751,8 +779,8 @@ int mggcn_engine_set_inputs(mggcn_engine_t *e, const float *X_host, const int32_
         if (e->swap_recorded) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->scopy, e->ev_swap, 0));  // WAR on the shadows
         if (X_host)
             MGGCN_CUDA_TRY(cudaMemcpy2DAsync(e->X_shadow, (size_t)e->ldX * 4, X_host, (size_t)e->sizes[0] * 4,
-                                             (size_t)e->sizes[0] * 4, (size_t)e->n, cudaMemcpyHostToDevice, e->scopy));
-        if (Y_host) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y_shadow, Y_host, (size_t)e->n * 4, cudaMemcpyHostToDevice, e->scopy));
+                                             (size_t)e->sizes[0] * 4, (size_t)e->n, cudaMemcpyDefault, e->scopy));
+        if (Y_host) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y_shadow, Y_host, (size_t)e->n * 4, cudaMemcpyDefault, e->scopy));
         MGGCN_CUDA_TRY(cudaEventRecord(e->ev_pref, e->scopy));
         e->pref_x = e->pref_x || X_host;
         e->pref_y = e->pref_y || Y_host;
@@ -762,8 +790,8 @@ int mggcn_engine_set_inputs(mggcn_engine_t *e, const float *X_host, const int32_
     cudaStream_t st = e->sc;
     if (X_host)
         MGGCN_CUDA_TRY(cudaMemcpy2DAsync(e->X, (size_t)e->ldX * 4, X_host, (size_t)e->sizes[0] * 4, (size_t)e->sizes[0] * 4,
-                                         (size_t)e->n, cudaMemcpyHostToDevice, st));
-    if (Y_host) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y, Y_host, (size_t)e->n * 4, cudaMemcpyHostToDevice, st));
+                                         (size_t)e->n, cudaMemcpyDefault, st));
+    if (Y_host) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y, Y_host, (size_t)e->n * 4, cudaMemcpyDefault, st));
     if (!async) MGGCN_CUDA_TRY(cudaStreamSynchronize(st));
     return MGGCN_OK;
 }
@@ -847,10 +875,56 @@ int mggcn_engine_adam_update(mggcn_engine_t *e, float lr, float beta1, float bet
     return adam(e, lr, beta1, beta2, wd, eps);
 }
 
+// Captures and instantiates the epoch graph (no launch).  Instantiation and upload allocate device
+// memory, which -- with peer access enabled -- waits for the peer GPUs to go idle: a process that
+// drives several engines must prepare all of them BEFORE it launches any (a launched engine spins in
+// its first barrier until its peers are launched too).
+static int ensure_graph(mggcn_engine_t *e, float lr, float beta1, float beta2, float wd, float eps) {
+    if (e->graph_exec && (lr != e->g_lr || beta1 != e->g_b1 || beta2 != e->g_b2 || wd != e->g_wd || eps != e->g_eps)) {
+        cudaGraphExecDestroy(e->graph_exec);
+        e->graph_exec = nullptr;
+    }
+    if (e->graph_exec) return MGGCN_OK;
+    cudaGraph_t graph = nullptr;
+    const uint64_t before = mggcn_launch_count();
+    MGGCN_CUDA_TRY(cudaStreamBeginCapture(e->sc, cudaStreamCaptureModeThreadLocal));
+    int rc = epoch_body(e, lr, beta1, beta2, wd, eps);
+    if (rc == MGGCN_OK && e->sm != e->sc) {
+        // join the exchange stream back into the origin stream before the capture ends
+        cudaError_t ce = cudaEventRecord(e->ev_join, e->sm);
+        if (ce == cudaSuccess) ce = cudaStreamWaitEvent(e->sc, e->ev_join, 0);
+        if (ce != cudaSuccess) rc = fail((int)ce, "graph join: %s", cudaGetErrorString(ce));
+    }
+    cudaError_t ce = cudaStreamEndCapture(e->sc, &graph);
+    if (rc) {
+        if (graph) cudaGraphDestroy(graph);
+        return rc;
+    }
+    if (ce != cudaSuccess) return fail((int)ce, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
+    e->launches_per_epoch = (int64_t)(mggcn_launch_count() - before);
+    g_launches.fetch_sub((uint64_t)e->launches_per_epoch, std::memory_order_relaxed);  // captured, not launched
+    ce = cudaGraphInstantiate(&e->graph_exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ce != cudaSuccess) return fail((int)ce, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
+    MGGCN_CUDA_TRY(cudaGraphUpload(e->graph_exec, e->sc));
+    MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
+    e->g_lr = lr; e->g_b1 = beta1; e->g_b2 = beta2; e->g_wd = wd; e->g_eps = eps;
+    return MGGCN_OK;
+}
+
+int mggcn_engine_prepare(mggcn_engine_t *e, float lr, float beta1, float beta2, float wd, float eps) {
+    if (!e) return fail(MGGCN_E_INVALID, "null engine");
+    TRY(check_ready(e));
+    TRY(set_dev(e));
+    if (!e->use_graph) return MGGCN_OK;
+    return ensure_graph(e, lr, beta1, beta2, wd, eps);
+}
+
 int mggcn_engine_epoch(mggcn_engine_t *e, float lr, float beta1, float beta2, float wd, float eps) {
     if (!e) return fail(MGGCN_E_INVALID, "null engine");
     TRY(check_ready(e));
     TRY(set_dev(e));
+    if (e->use_graph) TRY(ensure_graph(e, lr, beta1, beta2, wd, eps));
     TRY(swap_in_inputs(e));
     if (!e->use_graph) {
         const uint64_t before = mggcn_launch_count();
@@ -858,35 +932,7 @@ int mggcn_engine_epoch(mggcn_engine_t *e, float lr, float beta1, float beta2, fl
         e->launches_per_epoch = (int64_t)(mggcn_launch_count() - before);
         return MGGCN_OK;
     }
-    if (e->graph_exec && (lr != e->g_lr || beta1 != e->g_b1 || beta2 != e->g_b2 || wd != e->g_wd || eps != e->g_eps)) {
-        cudaGraphExecDestroy(e->graph_exec);
-        e->graph_exec = nullptr;
-    }
-    if (!e->graph_exec) {
-        cudaGraph_t graph = nullptr;
-        const uint64_t before = mggcn_launch_count();
-        MGGCN_CUDA_TRY(cudaStreamBeginCapture(e->sc, cudaStreamCaptureModeThreadLocal));
-        int rc = epoch_body(e, lr, beta1, beta2, wd, eps);
-        if (rc == MGGCN_OK && e->sm != e->sc) {
-            // join the exchange stream back into the origin stream before the capture ends
-            cudaError_t ce = cudaEventRecord(e->ev_join, e->sm);
-            if (ce == cudaSuccess) ce = cudaStreamWaitEvent(e->sc, e->ev_join, 0);
-            if (ce != cudaSuccess) rc = fail((int)ce, "graph join: %s", cudaGetErrorString(ce));
-        }
-        cudaError_t ce = cudaStreamEndCapture(e->sc, &graph);
-        if (rc) {
-            if (graph) cudaGraphDestroy(graph);
-            return rc;
-        }
-        if (ce != cudaSuccess) return fail((int)ce, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
-        e->launches_per_epoch = (int64_t)(mggcn_launch_count() - before);
-        ce = cudaGraphInstantiate(&e->graph_exec, graph, 0);
-        cudaGraphDestroy(graph);
-        if (ce != cudaSuccess) return fail((int)ce, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
-        e->g_lr = lr; e->g_b1 = beta1; e->g_b2 = beta2; e->g_wd = wd; e->g_eps = eps;
-    } else {
-        count_launch((uint64_t)e->launches_per_epoch);
-    }
+    count_launch((uint64_t)e->launches_per_epoch);
     MGGCN_CUDA_TRY(cudaGraphLaunch(e->graph_exec, e->sc));
     return MGGCN_OK;
 }
@@ -897,7 +943,7 @@ int mggcn_engine_sync(mggcn_engine_t *e) {
     MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
     if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sm));
     int err = 0;
-    MGGCN_CUDA_TRY(cudaMemcpy(&err, e->dev_err, sizeof err, cudaMemcpyDeviceToHost));
+    MGGCN_CUDA_TRY(cudaMemcpy(&err, e->dev_err, sizeof err, cudaMemcpyDefault));
     if (err) return fail(MGGCN_E_STATE, "peer barrier timed out (a rank is missing or died)");
     return MGGCN_OK;
 }
@@ -906,7 +952,7 @@ int mggcn_engine_loss(mggcn_engine_t *e, double *loss_sum, double *correct) {
     if (!e) return fail(MGGCN_E_INVALID, "null engine");
     TRY(set_dev(e));
     double h[2] = {0, 0};
-    MGGCN_CUDA_TRY(cudaMemcpyAsync(h, e->loss_out, sizeof h, cudaMemcpyDeviceToHost, e->sc));
+    MGGCN_CUDA_TRY(cudaMemcpyAsync(h, e->loss_out, sizeof h, cudaMemcpyDefault, e->sc));
     MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
     if (loss_sum) *loss_sum = h[0];
     if (correct) *correct = h[1];
@@ -942,7 +988,7 @@ int mggcn_engine_get(mggcn_engine_t *e, const char *name, float *out, size_t cap
     if (!out) return MGGCN_OK;
     if (cap < *count) return fail(MGGCN_E_INVALID, "buffer too small for %s", name);
     TRY(mggcn_engine_sync(e));
-    MGGCN_CUDA_TRY(cudaMemcpy2D(out, (size_t)c * 4, p, (size_t)ld * 4, (size_t)c * 4, (size_t)r, cudaMemcpyDeviceToHost));
+    MGGCN_CUDA_TRY(cudaMemcpy2D(out, (size_t)c * 4, p, (size_t)ld * 4, (size_t)c * 4, (size_t)r, cudaMemcpyDefault));
     return MGGCN_OK;
 }
 
@@ -953,7 +999,7 @@ int mggcn_engine_set(mggcn_engine_t *e, const char *name, const float *in, size_
     TRY(find_tensor(e, name, &p, &r, &c, &ld));
     if (count != (size_t)(r * c)) return fail(MGGCN_E_INVALID, "%s has %lld elements", name, (long long)(r * c));
     TRY(mggcn_engine_sync(e));
-    MGGCN_CUDA_TRY(cudaMemcpy2D(p, (size_t)ld * 4, in, (size_t)c * 4, (size_t)c * 4, (size_t)r, cudaMemcpyHostToDevice));
+    MGGCN_CUDA_TRY(cudaMemcpy2D(p, (size_t)ld * 4, in, (size_t)c * 4, (size_t)c * 4, (size_t)r, cudaMemcpyDefault));
     return MGGCN_OK;
 }
 

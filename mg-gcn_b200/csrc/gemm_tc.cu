@@ -539,11 +539,14 @@ split_plan plan_split(int ta, int64_t M, int64_t N, int64_t K, int bn) {
 template <int BN, bool A_MN, bool B_MN>
 int launch(cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const tc_args &g) {
     using C = cfg<BN>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the attribute is per device: one process may drive several GPUs (the mg_gcn CLI does)
+    static std::atomic<bool> attr_set[64];
+    int dev = 0;
+    MGGCN_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
         MGGCN_CUDA_TRY(cudaFuncSetAttribute(gemm_tc_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)C::SMEM_BYTES));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
     const int64_t total = (int64_t)g.mt * g.nt * g.nz;
     const unsigned grid = (unsigned)std::min<int64_t>(total, g_sm_count);

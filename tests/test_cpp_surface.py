@@ -1,0 +1,104 @@
+"""The C++ surface (mg-gcn_b200/cpp: header-only classes with the reference's names + the mg_gcn CLI).
+
+CPU: the surface builds, its host half passes the reference's container checks
+(test/test_matrix.cpp:10-121) on the committed fixtures, the CLI keeps the reference's option grammar.
+GPU: the reference's known-answer tests (test/test_gcn.cpp:98-249) replayed through the surface, and the
+CLI against the reference's own binary (oracle/_ref/mg_gcn_ref, built from /root/reference/src by
+oracle/Makefile) on the same generated dataset: per-epoch loss within 1e-4 over 10 epochs at equal P
+(north_star)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CPP = os.path.join(ROOT, "mg-gcn_b200", "cpp")
+BIN = os.path.join(CPP, "bin")
+REF = os.path.join(ROOT, "oracle", "_ref", "mg_gcn_ref")
+
+
+@pytest.fixture(scope="module")
+def cpp(mg):
+    if not (os.path.exists(os.path.join(BIN, "mg_gcn")) and os.path.exists(os.path.join(BIN, "test_surface"))):
+        r = subprocess.run(["make", "-C", CPP, "-j4"], capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    return BIN
+
+
+def run(cmd, **kw):
+    # a wiring mistake should fail in seconds, not after the 10 s default of every stage barrier
+    env = dict(os.environ, MGGCN_BARRIER_TIMEOUT_MS="3000")
+    return subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env, **kw)
+
+
+def test_host_half_of_the_surface(cpp):
+    r = run([os.path.join(cpp, "test_surface"), "host", os.path.join(ROOT, "tests", "golden")])
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "ok (0 failures)" in r.stdout
+
+
+def test_cli_option_grammar(cpp, tmp_path):
+    exe = os.path.join(cpp, "mg_gcn")
+    r = run([exe, "-h"])
+    assert r.returncode == 0 and "Usage:" in r.stdout and "-R" in r.stdout
+    r = run([exe, "-P", "1", "frobnicate"])                       # src/main.cpp:191-192: unknown command
+    assert r.returncode == 1 and "Error: uncaught exception" in r.stderr
+    r = run([exe, "train", str(tmp_path / "nowhere") + "/", "1", "16"])   # missing graph.bin -> matrix_error -> exit 1
+    assert r.returncode == 1 and "Error: uncaught exception" in r.stderr
+
+
+def epochs_of(stderr):
+    out = []
+    for line in stderr.splitlines():
+        f = line.split()
+        if len(f) == 4 and f[0].isdigit():
+            out.append((int(f[0]), float(f[1]), float(f[2]), float(f[3])))
+    return out
+
+
+@pytest.mark.gpu
+def test_reference_known_answers_through_the_surface(cpp, cuda):
+    r = run([os.path.join(cpp, "test_surface"), "gpu"])
+    assert r.returncode == 0, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_two_gpu_surface(cpp, cuda):
+    if cuda.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    r = run([os.path.join(cpp, "test_surface"), "dist"])
+    assert r.returncode == 0, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("P", [1, 2])
+@pytest.mark.parametrize("shape,hidden", [("reddit", [128, 128, 128]), ("proteins", [64, 64])])
+def test_cli_matches_reference_binary(mg, cpp, cuda, tmp_path, P, shape, hidden):
+    if cuda.cuda.device_count() < P:
+        pytest.skip(f"needs {P} GPUs")
+    if not os.path.exists(REF):
+        pytest.skip("oracle/_ref/mg_gcn_ref was not built (needs /root/reference at build time)")
+    A, X, Y, C = mg.generate(shape, seed=3, scale=0.04)
+    ds = tmp_path / "permuted" / shape
+    mg.write_dataset(str(ds), A, X, Y)
+    (tmp_path / "csvs").mkdir()
+    args = ["-P", str(P), "-R", "1", "-E", "10", "train", str(ds) + "/", str(len(hidden))] + [str(h) for h in hidden]
+    ref = run([REF] + args, cwd=tmp_path)
+    assert ref.returncode == 0, ref.stderr[-2000:]
+    for extra in ([], ["--eager"], ["--timers"]):
+        ours = run([os.path.join(cpp, "mg_gcn")] + extra + args, cwd=tmp_path)
+        assert ours.returncode == 0, ours.stdout[-1000:] + ours.stderr[-2000:]
+        # header lines are byte-identical (src/main.cpp:87-91)
+        assert ours.stderr.splitlines()[:3] == ref.stderr.splitlines()[:3]
+        eo, er = epochs_of(ours.stderr), epochs_of(ref.stderr)
+        assert len(eo) == len(er) == 10
+        for (e, lo, ao, _), (_, lr_, ar, _) in zip(eo, er):
+            assert abs(lo - lr_) <= 1e-4, (extra, e, lo, lr_)
+            assert abs(ao - ar) <= 5.0 / A.n + 1e-6, (extra, e, ao, ar)
+    # --timers wrote the reference's CSV schema "<epoch>_<gpu>_<name>:<ms>"
+    sizes = [X.shape[1]] + hidden + [mg.pad_classes(C, P)]
+    csv = tmp_path / "csvs" / ("permuted_" + shape + "".join(f"_{s}" for s in sizes) + f"_{P}.csv")
+    rows = csv.read_text().splitlines()
+    assert any(r.startswith("0_0_") and "matmul-spmm:" in r for r in rows)
+    assert all(float(r.rsplit(":", 1)[1]) >= 0 for r in rows)
