@@ -129,13 +129,32 @@ __global__ void xbarrier_kernel(peer_table pt, uint32_t *tickets, int slot, int 
         const long long t0 = clock64();
         while ((int32_t)(*src - ticket) < 0) {
             if (clock64() - t0 > timeout_cycles) {
-                *err = 1;
+                if (atomicCAS(err, 0, 1) == 0) {  // first failure wins: which flag was missing
+                    err[1] = slot * kMaxRanks + t;
+                    err[2] = (int)*src;
+                    err[3] = (int)ticket;
+                }
                 break;
             }
             __nanosleep(200);
         }
         __threadfence_system();
     }
+}
+
+// SM-driven pull of a peer's feature block over NVLink (128-bit loads from peer-mapped memory).
+// Used instead of a copy-engine transfer when the peer GPU is driven by THIS process and the epoch
+// is enqueued eagerly: there a cross-device cudaMemcpyAsync waiting behind this GPU's stage barrier
+// holds back the peer's own launches (measured on B200: the peer's barrier kernel did not start
+// until the waiting one timed out), which a kernel that touches only this GPU's queues cannot do.
+__global__ void __launch_bounds__(512) pull_copy_kernel(const float4 *__restrict__ src, float4 *__restrict__ dst, size_t n4) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n4; i += 4 * stride) {
+        const float4 a = src[i], b = src[i + stride], c = src[i + 2 * stride], d = src[i + 3 * stride];
+        dst[i] = a; dst[i + stride] = b; dst[i + 2 * stride] = c; dst[i + 3 * stride] = d;
+    }
+    for (; i < n4; i += stride) dst[i] = src[i];
 }
 
 struct grad_peers {
@@ -234,6 +253,8 @@ struct mggcn_engine {
     // p2p
     char *peer_arena[kMaxRanks] = {nullptr};
     bool peer_opened[kMaxRanks] = {false};
+    bool peer_inproc[kMaxRanks] = {false};  // the peer's engine lives in this process
+    bool capturing = false;
     bool connected = false;
     int barrier_next = 0;
 
@@ -343,8 +364,15 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
             const size_t count = (size_t)a.cols * (size_t)ld;
             TRY(timer_begin(e, tname + std::to_string(s) + "_matmul-bcast", e->sm, &t_x));
             if (e->p2p) {
-                MGGCN_CUDA_TRY(cudaMemcpyAsync(e->stage[s & 1], e->peer_arena[blk] + off, count * sizeof(float),
-                                               cudaMemcpyDeviceToDevice, e->sm));
+                if (e->peer_inproc[blk] && !e->capturing) {
+                    // count is a multiple of 4 floats (ld is), both ends are 256-byte aligned arena carvings
+                    pull_copy_kernel<<<64, 512, 0, e->sm>>>(reinterpret_cast<const float4 *>(e->peer_arena[blk] + off),
+                                                            reinterpret_cast<float4 *>(e->stage[s & 1]), count / 4);
+                    MGGCN_LAUNCH_CHECK();
+                } else {
+                    MGGCN_CUDA_TRY(cudaMemcpyAsync(e->stage[s & 1], e->peer_arena[blk] + off, count * sizeof(float),
+                                                   cudaMemcpyDeviceToDevice, e->sm));
+                }
                 src = e->stage[s & 1];
                 TRACE(e->rank, "dist_spmm: peer copy enqueued");
             } else if (blk == e->rank) {
@@ -836,6 +864,7 @@ int mggcn_engine_comm_connect(mggcn_engine_t *e, const void *handles, size_t len
                 return fail((int)pe, "cudaDeviceEnablePeerAccess(%d): %s", attr.device, cudaGetErrorString(pe));
             cudaGetLastError();
             e->peer_arena[r] = reinterpret_cast<char *>((uintptr_t)ptr);
+            e->peer_inproc[r] = true;
         } else {
             cudaIpcMemHandle_t h;
             memcpy(&h, hs + (size_t)r * need + 16, sizeof h);
@@ -888,7 +917,9 @@ static int ensure_graph(mggcn_engine_t *e, float lr, float beta1, float beta2, f
     cudaGraph_t graph = nullptr;
     const uint64_t before = mggcn_launch_count();
     MGGCN_CUDA_TRY(cudaStreamBeginCapture(e->sc, cudaStreamCaptureModeThreadLocal));
+    e->capturing = true;
     int rc = epoch_body(e, lr, beta1, beta2, wd, eps);
+    e->capturing = false;
     if (rc == MGGCN_OK && e->sm != e->sc) {
         // join the exchange stream back into the origin stream before the capture ends
         cudaError_t ce = cudaEventRecord(e->ev_join, e->sm);
@@ -942,9 +973,11 @@ int mggcn_engine_sync(mggcn_engine_t *e) {
     TRY(set_dev(e));
     MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
     if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sm));
-    int err = 0;
-    MGGCN_CUDA_TRY(cudaMemcpy(&err, e->dev_err, sizeof err, cudaMemcpyDefault));
-    if (err) return fail(MGGCN_E_STATE, "peer barrier timed out (a rank is missing or died)");
+    int err[4] = {0, 0, 0, 0};
+    MGGCN_CUDA_TRY(cudaMemcpy(err, e->dev_err, sizeof err, cudaMemcpyDefault));
+    if (err[0])
+        return fail(MGGCN_E_STATE, "peer barrier timed out (a rank is missing or died): rank %d, barrier %d waited for "
+                    "rank %d's ticket %d, saw %d", e->rank, err[1] / kMaxRanks, err[1] % kMaxRanks, err[3], err[2]);
     return MGGCN_OK;
 }
 

@@ -97,7 +97,7 @@ def test_cli_matches_reference_binary(mg, cpp, cuda, tmp_path, P, shape, hidden)
             assert abs(lo - lr_) <= 1e-4, (extra, e, lo, lr_)
             assert abs(ao - ar) <= 5.0 / A.n + 1e-6, (extra, e, ao, ar)
     # --timers wrote the reference's CSV schema "<epoch>_<gpu>_<name>:<ms>"
-    sizes = [X.shape[1]] + hidden + [mg.pad_classes(C, P)]
+    sizes = [X.shape[1]] + hidden + [C]   # the file is named before the class count is padded (src/main.cpp:100-111,135)
     csv = tmp_path / "csvs" / ("permuted_" + shape + "".join(f"_{s}" for s in sizes) + f"_{P}.csv")
     rows = csv.read_text().splitlines()
     assert any(r.startswith("0_0_") and "matmul-spmm:" in r for r in rows)
