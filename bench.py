@@ -230,6 +230,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:  # every rank pre-processes the graph: share the host cores instead of oversubscribing them
+        os.environ.setdefault("OMP_NUM_THREADS", str(max(1, (os.cpu_count() or 8) // world)))
     mg = load_package()
     if args.impl == "reference":
         run_reference(args, mg, rank)
