@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--shape", default="reddit")
     ap.add_argument("--hidden", type=int, nargs="+", default=[128, 128, 128])
-    ap.add_argument("--comm", default="p2p", choices=["nccl", "p2p"])
+    ap.add_argument("--comm", default="p2p", choices=["nccl", "p2p", "p2p-staged"])
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the graph (debugging only; marks the line)")
@@ -231,7 +231,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:  # every rank pre-processes the graph: share the host cores instead of oversubscribing them
-        os.environ.setdefault("OMP_NUM_THREADS", str(max(1, (os.cpu_count() or 8) // world)))
+        if os.environ.get("OMP_NUM_THREADS", "1") == "1":  # torchrun's default of 1 makes the host prep 8x slower
+            os.environ["OMP_NUM_THREADS"] = str(max(1, (os.cpu_count() or 8) // world))
     mg = load_package()
     if args.impl == "reference":
         run_reference(args, mg, rank)
@@ -252,7 +253,7 @@ def main():
     N, nnz = A.n, A.nnz
     sizes = [X.shape[1]] + args.hidden + [mg.pad_classes(C, P)]
     nccl_id = None
-    comm = mg.COMM_P2P if args.comm == "p2p" else mg.COMM_NCCL
+    comm = {"p2p": mg.COMM_P2P, "p2p-staged": mg.COMM_P2P_STAGED, "nccl": mg.COMM_NCCL}[args.comm]
     if P > 1 and comm == mg.COMM_NCCL:
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
@@ -263,7 +264,7 @@ def main():
         nccl_id = bytes(idt.cpu().numpy().tobytes())
     eng, A_T = mg.build_rank_engine(A, sizes, world=P, rank=rank, device=local, use_graph=not args.no_graph,
                                     nccl_id=nccl_id, comm=comm, overlap=not args.no_overlap)
-    if P > 1 and comm == mg.COMM_P2P:
+    if P > 1 and comm != mg.COMM_NCCL:
         h = eng.comm_handle()
         ht = torch.frombuffer(bytearray(h), dtype=torch.uint8).cuda()
         allh = [torch.empty_like(ht) for _ in range(P)]
@@ -337,11 +338,14 @@ def main():
     # forward SpMMs of width 128 through the forward operand (layers whose SpMM width is hidden[0])
     n_loc = r1 - r0
     F = args.hidden[0]
-    if P == 1:
+    fused = P > 1 and args.comm == "p2p"
+    dom_nnz = A_T.nnz / (P * P if (P > 1 and not fused) else P)
+    if P == 1 or fused:
         dom = [v for k, v in med.items() if k.endswith("_0_matmul-spmm") and not k.startswith(f"{len(sizes) - 2}_")]
         dom_ms = float(np.mean(dom)) if dom else float("nan")
-        alg = spmm_alg_bytes(N, N, A_T.nnz, F)
-        dom_name = f"spmm_kernel<32,1,4> forward, F={F}, whole matrix"
+        alg = spmm_alg_bytes(n_loc, N, dom_nnz, F)
+        dom_name = (f"spmm_kernel<32,1,4> forward, F={F}, whole matrix" if P == 1 else
+                    f"spmm_kernel<32,1,4,gathered> forward, F={F}, block row {n_loc}x{N} in one launch (waits on-device for the peers' blocks)")
     else:
         dom = [v for k, v in med.items() if k.endswith("_matmul-spmm-stage") and k.split("_")[1] == "0"
                and not k.startswith(f"{len(sizes) - 2}_")]
@@ -393,8 +397,8 @@ def main():
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)",
                      "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                      "alg_bytes_per_launch": alg, "launch_ms": dom_ms,
-                     "gather_GBps": (A_T.nnz / (P * P if P > 1 else 1) * F * 4 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 else None,
-                     "GFLOPs": (2 * A_T.nnz / (P * P if P > 1 else 1) * F / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 else None,
+                     "gather_GBps": (dom_nnz * F * 4 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 else None,
+                     "GFLOPs": (2 * dom_nnz * F / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 else None,
                      "note": "B (119 MB at F=128) is gathered avg-degree (~490) times: the kernel is L1/L2-gather bound, "
                              "not HBM bound (SURVEY.md hard part 1); gather_GBps is the operand traffic it sustains"},
         "breakdown_ms": {"spmm": spmm_ms, "gemm": gemm_ms, "exchange": xfer_ms,

@@ -99,6 +99,24 @@ MGGCN_API int mggcn_spmm_csr_f32_i64(mggcn_stream_t stream, int64_t rows, int64_
                                      const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan,
                                      void *ws);
 
+/* a3 (device side). The aggregation over a whole block row of the 1-D partition while the feature
+ * blocks of the other ranks are still arriving:  C = alpha * A[rank][:] * H + beta * C.
+ *  A: rows x cols CSR with GLOBAL column ids, every row stored in stage order (own block first, then
+ *     blocks rank+1, rank+2, ... cyclically; ascending columns inside a block).
+ *  gathered: cols x F (leading dimension ld), global row order, filled block by block by copy engines /
+ *     peers while the kernel runs; stage_flags[s] (s = 1..P-1, device memory) becomes non-zero after the
+ *     block of stage s = block (rank+s)%P is complete.  B_own: this rank's own rows (same ld), complete
+ *     at launch.  cuts: P+1 row cuts of the partition (host memory).  err (device, nullable) is raised
+ *     to 2 if a flag does not arrive within ~4 s of SM clock -- the launch never hangs. */
+MGGCN_API int mggcn_spmm_gathered_f32_i32(mggcn_stream_t stream, int64_t rows, int64_t cols,
+                                          const uint32_t *rowptr, const uint32_t *colidx,
+                                          const float *vals, const float *gathered,
+                                          const float *B_own, int64_t ld, float *C, int64_t ldc, int F,
+                                          float alpha, float beta, int P, int rank,
+                                          const uint32_t *cuts, const uint32_t *stage_flags, int *err,
+                                          const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan,
+                                          void *ws);
+
 /* a2. replaces get_matmul_buffer / cusparseSpMM_bufferSize (src/cuda_utils.hpp:94-102):
  * the plan is built once per matrix (block) from a HOST copy of the row pointers; it owns a
  * small device-side item list.  split_nnz <= 0 selects the default row-split threshold. */
@@ -273,10 +291,15 @@ typedef struct {
  *  NCCL: root-rotating ncclBroadcast per stage, exactly the reference's schedule
  *        (src/dist_matrix.hpp:458-467), and one ncclAllReduce for the packed gradients;
  *  P2P:  every rank pulls block (rank+s)%P at stage s out of the owner's arena through
- *        peer-mapped memory (NVLink copy engines), flag barriers in peer memory for ordering, and
- *        a rank-ordered sum of the peers' gradients.  Needs mggcn_engine_comm_handle /
- *        mggcn_engine_comm_connect after create. */
-enum { MGGCN_COMM_NCCL = 0, MGGCN_COMM_P2P = 1 };
+ *        peer-mapped memory (NVLink copy engines) into its place in an all-gather buffer and publishes
+ *        a stage flag behind it; ONE SpMM launch per aggregation works through this rank's whole block
+ *        row in stage order and waits (on the device) only for blocks that have not landed yet, so
+ *        transfer and multiplication overlap without per-stage launches.  Flag barriers in peer
+ *        memory order the ranks; gradients are summed in rank order from the peers' arenas.  Needs
+ *        mggcn_engine_comm_handle / mggcn_engine_comm_connect after create.
+ *  P2P_STAGED: the same transfers with the reference's structure -- one SpMM launch per stage on a
+ *        double-buffered staging area (src/cuda_utils.hpp:57-92). */
+enum { MGGCN_COMM_NCCL = 0, MGGCN_COMM_P2P = 1, MGGCN_COMM_P2P_STAGED = 2 };
 
 MGGCN_API int mggcn_nccl_unique_id(void *id128);
 MGGCN_API int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out);

@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libmggcn.so")
 INCLUDE = os.path.join(os.path.dirname(_HERE), "include", "mggcn.h")
 
 EPI_NONE, EPI_LEAKY_RELU, EPI_LEAKY_RELU_BWD = 0, 1, 2
-COMM_NCCL, COMM_P2P = 0, 1
+COMM_NCCL, COMM_P2P, COMM_P2P_STAGED = 0, 1, 2
 
 
 class MggcnError(RuntimeError):
@@ -66,6 +66,8 @@ _SIGS = {
                                          C.POINTER(Epilogue), _vp, _vp]),
     "mggcn_spmm_csr_f32_i64": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _i64, _i32, _f32, _f32,
                                          C.POINTER(Epilogue), _vp, _vp]),
+    "mggcn_spmm_gathered_f32_i32": (C.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, _i32, _f32, _f32,
+                                              _i32, _i32, _vp, _vp, _vp, C.POINTER(Epilogue), _vp, _vp]),
     "mggcn_spmm_plan_create_i32": (C.c_int, [_i64, _vp, _i32, C.POINTER(_vp)]),
     "mggcn_spmm_plan_create_i64": (C.c_int, [_i64, _vp, _i32, C.POINTER(_vp)]),
     "mggcn_spmm_plan_workspace_bytes": (_sz, [_vp, _i32]),

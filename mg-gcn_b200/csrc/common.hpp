@@ -28,6 +28,17 @@ static inline uint64_t mix64(uint64_t x) {
 static inline uint64_t hash2(uint64_t seed, uint64_t i) { return mix64(mix64(seed) ^ (i * 0xD6E8FEB86659FD93ull)); }
 static inline double u01(uint64_t h) { return (double)(h >> 11) * (1.0 / 9007199254740992.0); }
 
+// Description of the gathered multi-GPU operand of the SpMM (csrc/spmm.cu, used by csrc/engine.cu and
+// mggcn_spmm_gathered_f32_i32): see spmm_args::g.
+struct spmm_gather {
+    const uint32_t *flags = nullptr;  // P words; flags[s] != 0: the block of stage s is in place (flags[0] unused)
+    const float *B_own = nullptr;     // this rank's own rows (stage 0), leading dimension = ldb
+    uint32_t own_lo = 0, own_n = 0;   // global column range of the own rows
+    int P = 1, rank = 0;
+    int *err = nullptr;               // raised to 2 when a stage flag never arrives
+    uint32_t cuts[16] = {0};          // cuts[i] = first global column of block i (i < P), 0xFFFFFFFF beyond
+};
+
 }  // namespace mggcn
 
 #ifdef __CUDACC__

@@ -16,6 +16,7 @@
 //     kernel that sums the peers' packed gradients in rank order) and Adam is one launch;
 //   * the whole epoch is captured into one CUDA graph (use_graph), removing ~100 launches and all
 //     the event bookkeeping of src/cuda_utils.hpp:61-91 from the host path.
+#include <cuda.h>  // CUstream / CUdeviceptr for cuStreamWriteValue32 (resolved at run time, no -lcuda)
 #include <dlfcn.h>
 #include <nccl.h>
 #include <unistd.h>
@@ -27,6 +28,12 @@
 #include "common.hpp"
 
 using namespace mggcn;
+
+namespace mggcn {
+int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx,
+                  const float *vals, const float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
+                  float beta, const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws, const spmm_gather &g);
+}
 
 namespace {
 
@@ -157,6 +164,36 @@ __global__ void __launch_bounds__(512) pull_copy_kernel(const float4 *__restrict
     for (; i < n4; i += stride) dst[i] = src[i];
 }
 
+// Publishes a stage flag behind the transfers queued on `st`.  A stream memory operation is executed by the
+// GPU's front end: unlike a small memset (which may be a kernel) it needs no SM slot, so it cannot be starved by
+// a grid of CTAs that wait for this very flag.
+typedef CUresult (*stream_write32_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+stream_write32_fn stream_write32() {
+    static stream_write32_fn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (getenv("MGGCN_FLAG_MEMSET") || cudaGetDriverEntryPoint("cuStreamWriteValue32", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            p = nullptr;
+        }
+        return reinterpret_cast<stream_write32_fn>(p);
+    }();
+    return fn;
+}
+bool g_memop_in_capture = true;  // cleared when a capture that used stream memory operations fails
+int publish_flag(cudaStream_t st, uint32_t *flag, bool capturing) {
+    stream_write32_fn w = capturing && !g_memop_in_capture ? nullptr : stream_write32();
+    if (w) {
+        const CUresult r = w(reinterpret_cast<CUstream>(st), reinterpret_cast<CUdeviceptr>(flag), 1u, 0u);
+        if (r == CUDA_SUCCESS) return MGGCN_OK;
+        if (r != CUDA_ERROR_NOT_SUPPORTED && r != CUDA_ERROR_STREAM_CAPTURE_UNSUPPORTED)
+            return fail((int)r, "cuStreamWriteValue32 failed (%d)", (int)r);
+    }
+    MGGCN_CUDA_TRY(cudaMemsetAsync(flag, 0x01, sizeof(uint32_t), st));
+    return MGGCN_OK;
+}
+
 struct grad_peers {
     const float *g[kMaxRanks];
 };
@@ -240,6 +277,12 @@ struct mggcn_engine {
     int32_t *Y = nullptr;
     int64_t ldX = 0;
     float *HW = nullptr, *G[2] = {nullptr, nullptr}, *stage[2] = {nullptr, nullptr};
+    // gathered form (p2p back-end): one launch per aggregation over the whole block row; the copy engines
+    // fill `gather` (all ranks' rows, global order) while the kernel already works on the stages that landed
+    bool fused = false;
+    float *gather = nullptr;
+    uint32_t *stage_flags = nullptr;
+    cudaEvent_t ev_bar = nullptr, ev_copied = nullptr;
     int64_t maxw = 0, max_block_rows = 0;
     float *params = nullptr, *grads = nullptr, *gsum = nullptr, *adam_m = nullptr, *adam_v = nullptr;
     size_t n_params = 0, n_weights = 0;
@@ -347,6 +390,70 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
         return MGGCN_OK;
     }
     const size_t off = (size_t)(reinterpret_cast<const char *>(B) - e->arena);
+    if (e->fused) {
+        // compute stream: clear the stage flags; exchange stream: barrier (every rank's B is complete), then
+        // pull block (rank+s)%P into its place of the all-gather buffer and publish flag s behind it.  The
+        // aggregation is ONE launch, issued as soon as the barrier has passed: it starts on the own block and
+        // waits on the device for a stage only if its block has not landed yet.
+        const adj_block &a = e->adj[which][0];
+        int t_all, t_x;
+        MGGCN_CUDA_TRY(cudaMemsetAsync(e->stage_flags, 0, 16 * sizeof(uint32_t), e->sc));
+        MGGCN_CUDA_TRY(cudaEventRecord(e->ev_ready, e->sc));
+        if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sm, e->ev_ready, 0));
+        TRY(xbarrier(e, e->sm));
+        if (e->sm != e->sc) {
+            // the barrier kernel must not queue behind a grid of waiting CTAs: the SpMM starts after it
+            MGGCN_CUDA_TRY(cudaEventRecord(e->ev_bar, e->sm));
+            MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_bar, 0));
+        }
+        TRY(timer_begin(e, tname + "matmul-spmm", e->sc, &t_all));
+        bool sm_copies = false;
+        for (int s = 1; s < P; ++s) {
+            const int blk = (e->rank + s) % P;
+            const size_t rows_b = (size_t)e->cuts[blk + 1] - (size_t)e->cuts[blk];
+            const size_t count = rows_b * (size_t)ld;
+            float *dst = e->gather + (size_t)e->cuts[blk] * (size_t)ld;
+            TRY(timer_begin(e, tname + std::to_string(s) + "_matmul-bcast", e->sm, &t_x));
+            if (e->peer_inproc[blk] && !e->capturing) {
+                pull_copy_kernel<<<64, 512, 0, e->sm>>>(reinterpret_cast<const float4 *>(e->peer_arena[blk] + off),
+                                                        reinterpret_cast<float4 *>(dst), count / 4);
+                MGGCN_LAUNCH_CHECK();
+                sm_copies = true;
+            } else {
+                MGGCN_CUDA_TRY(cudaMemcpyAsync(dst, e->peer_arena[blk] + off, count * sizeof(float),
+                                               cudaMemcpyDeviceToDevice, e->sm));
+            }
+            TRY(publish_flag(e->sm, e->stage_flags + s, e->capturing));
+            TRY(timer_end(e, e->sm, t_x));
+        }
+        if (sm_copies || e->sm == e->sc) {
+            // copies done by SMs (eager mode with in-process peers) cannot share the GPU with CTAs that wait
+            // for them: finish the transfers first
+            if (e->sm != e->sc) {
+                MGGCN_CUDA_TRY(cudaEventRecord(e->ev_copied, e->sm));
+                MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_copied, 0));
+            }
+        }
+        spmm_gather g;
+        g.flags = e->stage_flags;
+        g.B_own = B;
+        g.own_lo = e->cuts[e->rank];
+        g.own_n = e->cuts[e->rank + 1] - e->cuts[e->rank];
+        g.P = P;
+        g.rank = e->rank;
+        g.err = e->dev_err;
+        for (int i = 0; i < 16; ++i) g.cuts[i] = i < P ? e->cuts[i] : 0xFFFFFFFFu;
+        TRY(spmm_gathered(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, e->gather, ld, C, ld, (int)F, 1.f, 0.f, epi,
+                          a.plan, e->ws_spmm, g));
+        TRY(timer_end(e, e->sc, t_all));
+        // nobody may overwrite B before every peer has pulled it
+        TRY(xbarrier(e, e->sm));
+        if (e->sm != e->sc) {
+            MGGCN_CUDA_TRY(cudaEventRecord(e->ev_done, e->sm));
+            MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_done, 0));
+        }
+        return MGGCN_OK;
+    }
     MGGCN_CUDA_TRY(cudaEventRecord(e->ev_ready, e->sc));
     if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sm, e->ev_ready, 0));
     TRACE(e->rank, "dist_spmm: events recorded");
@@ -592,7 +699,8 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     e->overlap = cfg->overlap != 0;
     e->exact = cfg->exact_grads != 0;
     e->use_graph = cfg->use_graph != 0;
-    e->p2p = cfg->comm_backend == MGGCN_COMM_P2P && cfg->world > 1;
+    e->p2p = (cfg->comm_backend == MGGCN_COMM_P2P || cfg->comm_backend == MGGCN_COMM_P2P_STAGED) && cfg->world > 1;
+    e->fused = e->p2p && cfg->comm_backend == MGGCN_COMM_P2P && !getenv("MGGCN_STAGED");
     e->timers_on = cfg->timers != 0 && !e->use_graph;
     e->slope = cfg->lrelu_slope;
     e->N = cfg->n_global;
@@ -625,6 +733,8 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     E_CUDA(cudaEventCreateWithFlags(&e->ev_ready, cudaEventDisableTiming));
     E_CUDA(cudaEventCreateWithFlags(&e->ev_done, cudaEventDisableTiming));
     E_CUDA(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+    E_CUDA(cudaEventCreateWithFlags(&e->ev_bar, cudaEventDisableTiming));
+    E_CUDA(cudaEventCreateWithFlags(&e->ev_copied, cudaEventDisableTiming));
     e->ev_xfer.resize(e->P);
     e->ev_spmm.resize(e->P);
     for (int i = 0; i < e->P; ++i) {
@@ -669,7 +779,10 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     need(n * (size_t)e->maxw * 4);                                 // HW
     need(n * (size_t)e->maxw * 4);                                 // G0
     need(n * (size_t)e->maxw * 4);                                 // G1
-    if (e->P > 1) {
+    if (e->fused) {
+        need((size_t)e->N * (size_t)e->maxw * 4);
+        need(64);
+    } else if (e->P > 1) {
         need((size_t)e->max_block_rows * (size_t)e->maxw * 4);
         need((size_t)e->max_block_rows * (size_t)e->maxw * 4);
     }
@@ -695,7 +808,10 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     e->HW = carve<float>(cur, n * (size_t)e->maxw);
     e->G[0] = carve<float>(cur, n * (size_t)e->maxw);
     e->G[1] = carve<float>(cur, n * (size_t)e->maxw);
-    if (e->P > 1) {
+    if (e->fused) {
+        e->gather = carve<float>(cur, (size_t)e->N * (size_t)e->maxw);
+        e->stage_flags = carve<uint32_t>(cur, 16);
+    } else if (e->P > 1) {
         e->stage[0] = carve<float>(cur, (size_t)e->max_block_rows * (size_t)e->maxw);
         e->stage[1] = carve<float>(cur, (size_t)e->max_block_rows * (size_t)e->maxw);
     }
@@ -758,7 +874,53 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
     if (!e || which < 0 || which > 1 || !blk_rowptr || !blk_colidx || !blk_vals) return fail(MGGCN_E_INVALID, "bad argument");
     TRY(set_dev(e));
     size_t ws = e->ws_spmm_bytes;
-    for (int j = 0; j < e->P; ++j) {
+    if (e->fused) {
+        // one CSR over this rank's whole block row: global column ids, every row in stage order
+        // (own block, then blocks rank+1, rank+2, ... cyclically), so one launch can follow the transfers
+        adj_block &a = e->adj[which][0];
+        if (a.plan) { mggcn_spmm_plan_destroy(a.plan); a.plan = nullptr; }
+        if (a.rowptr) { cudaFree(a.rowptr); a.rowptr = nullptr; }
+        if (a.colidx) { cudaFree(a.colidx); a.colidx = nullptr; }
+        if (a.vals) { cudaFree(a.vals); a.vals = nullptr; }
+        const int P = e->P;
+        const int64_t n = e->n;
+        std::vector<uint64_t> rp((size_t)n + 1, 0);
+        for (int64_t r = 0; r < n; ++r) {
+            uint64_t c = 0;
+            for (int j = 0; j < P; ++j) c += blk_rowptr[j][r + 1] - blk_rowptr[j][r];
+            rp[(size_t)r + 1] = rp[(size_t)r] + c;
+        }
+        const uint64_t nnz = rp[(size_t)n];
+        if (nnz > 0xFFFFFFFFull) return fail(MGGCN_E_UNSUPPORTED, "block row has more than 2^32 entries");
+        std::vector<uint32_t> ci((size_t)std::max<uint64_t>(nnz, 1));
+        std::vector<float> va((size_t)std::max<uint64_t>(nnz, 1));
+#pragma omp parallel for schedule(static)
+        for (int64_t r = 0; r < n; ++r) {
+            uint64_t o = rp[(size_t)r];
+            for (int st = 0; st < P; ++st) {
+                const int j = (e->rank + st) % P;
+                const uint32_t base = e->cuts[j];
+                for (uint64_t k = blk_rowptr[j][r]; k < blk_rowptr[j][r + 1]; ++k, ++o) {
+                    ci[(size_t)o] = blk_colidx[j][k] + base;
+                    va[(size_t)o] = blk_vals[j][k];
+                }
+            }
+        }
+        std::vector<uint32_t> rp32((size_t)n + 1);
+        for (int64_t r = 0; r <= n; ++r) rp32[(size_t)r] = (uint32_t)rp[(size_t)r];
+        a.rows = n;
+        a.cols = e->N;
+        a.nnz = (int64_t)nnz;
+        MGGCN_CUDA_TRY(cudaMalloc(&a.rowptr, rp32.size() * 4));
+        MGGCN_CUDA_TRY(cudaMemcpy(a.rowptr, rp32.data(), rp32.size() * 4, cudaMemcpyDefault));
+        MGGCN_CUDA_TRY(cudaMalloc(&a.colidx, ci.size() * 4));
+        MGGCN_CUDA_TRY(cudaMalloc(&a.vals, va.size() * 4));
+        MGGCN_CUDA_TRY(cudaMemcpy(a.colidx, ci.data(), (size_t)nnz * 4, cudaMemcpyDefault));
+        MGGCN_CUDA_TRY(cudaMemcpy(a.vals, va.data(), (size_t)nnz * 4, cudaMemcpyDefault));
+        TRY(mggcn_spmm_plan_create_i32(a.rows, rp32.data(), 0, &a.plan));
+        ws = std::max(ws, mggcn_spmm_plan_workspace_bytes(a.plan, (int)e->maxw));
+    }
+    for (int j = 0; j < e->P && !e->fused; ++j) {
         adj_block &a = e->adj[which][j];
         if (a.plan) { mggcn_spmm_plan_destroy(a.plan); a.plan = nullptr; }
         if (a.rowptr) { cudaFree(a.rowptr); a.rowptr = nullptr; }
@@ -927,6 +1089,14 @@ static int ensure_graph(mggcn_engine_t *e, float lr, float beta1, float beta2, f
         if (ce != cudaSuccess) rc = fail((int)ce, "graph join: %s", cudaGetErrorString(ce));
     }
     cudaError_t ce = cudaStreamEndCapture(e->sc, &graph);
+    if ((rc || ce != cudaSuccess) && e->fused && g_memop_in_capture && stream_write32()) {
+        // this driver does not capture stream memory operations: capture again with memsets as flags
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        g_memop_in_capture = false;
+        g_launches.fetch_sub(mggcn_launch_count() - before, std::memory_order_relaxed);
+        return ensure_graph(e, lr, beta1, beta2, wd, eps);
+    }
     if (rc) {
         if (graph) cudaGraphDestroy(graph);
         return rc;
@@ -975,6 +1145,7 @@ int mggcn_engine_sync(mggcn_engine_t *e) {
     if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sm));
     int err[4] = {0, 0, 0, 0};
     MGGCN_CUDA_TRY(cudaMemcpy(err, e->dev_err, sizeof err, cudaMemcpyDefault));
+    if (err[0] == 2) return fail(MGGCN_E_STATE, "a feature block of a peer never arrived (stage flag timed out)");
     if (err[0])
         return fail(MGGCN_E_STATE, "peer barrier timed out (a rank is missing or died): rank %d, barrier %d waited for "
                     "rank %d's ticket %d, saw %d", e->rank, err[1] / kMaxRanks, err[1] % kMaxRanks, err[3], err[2]);
@@ -1090,6 +1261,8 @@ void mggcn_engine_destroy(mggcn_engine_t *e) {
     if (e->ev_ready) cudaEventDestroy(e->ev_ready);
     if (e->ev_done) cudaEventDestroy(e->ev_done);
     if (e->ev_join) cudaEventDestroy(e->ev_join);
+    if (e->ev_bar) cudaEventDestroy(e->ev_bar);
+    if (e->ev_copied) cudaEventDestroy(e->ev_copied);
     if (e->ev_pref) cudaEventDestroy(e->ev_pref);
     if (e->ev_swap) cudaEventDestroy(e->ev_swap);
     if (e->X_shadow) cudaFree(e->X_shadow);

@@ -82,6 +82,10 @@ struct spmm_args {
     float alpha, beta;
     mggcn_epilogue epi;
     int policy;
+    // "gathered" multi-GPU form (GATHER kernels only): B is the all-gather buffer in global row order that
+    // the copy engines are still filling while the kernel runs; columns in [own_lo, own_lo + own_n) are this
+    // rank's own rows and are read from B_own instead.  flags[s] != 0 once the block of stage s has landed.
+    mggcn::spmm_gather g;
 };
 
 __device__ __forceinline__ uint64_t make_policy_evict_last() {
@@ -126,6 +130,36 @@ __device__ __forceinline__ float ldg_stream_f32(const float *p, uint64_t pol) {
     return r;
 }
 
+__device__ __forceinline__ float4 ldg_coherent_f4(const float *p, uint64_t pol) {
+    float4 r;
+    asm volatile("ld.global.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p), "l"(pol)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ float ldg_coherent_f1(const float *p, uint64_t pol) {
+    float r;
+    asm volatile("ld.global.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(r) : "l"(p), "l"(pol) : "memory");
+    return r;
+}
+// Spins until the copy engine has published stage `s` (flags are written after the block's data on
+// the same stream).  Bounded: about 4 s of SM clock, then the error word is raised and the kernel
+// carries on with whatever is there, so a wiring mistake cannot hang the GPU.
+__device__ __forceinline__ void wait_stage(const uint32_t *flag, int *err) {
+    uint32_t v;
+    const long long t0 = clock64();
+    for (;;) {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if (v) break;
+        if (clock64() - t0 > 8000000000ll) {
+            if (err) *err = 2;
+            break;
+        }
+        __nanosleep(64);
+    }
+}
+
 template <int VEC>
 struct vec_t;
 template <>
@@ -135,11 +169,16 @@ struct vec_t<4> {
         float4 t = ldg_f4(p, pol);
         v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
     }
+    __device__ __forceinline__ void load_coherent(const float *p, uint64_t pol) {
+        float4 t = ldg_coherent_f4(p, pol);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    }
 };
 template <>
 struct vec_t<1> {
     float v[1];
     __device__ __forceinline__ void load(const float *p, uint64_t pol) { v[0] = ldg_f1(p, pol); }
+    __device__ __forceinline__ void load_coherent(const float *p, uint64_t pol) { v[0] = ldg_coherent_f1(p, pol); }
 };
 
 __device__ __forceinline__ float apply_epilogue(float x, const mggcn_epilogue &e, int64_t row, int col) {
@@ -158,7 +197,7 @@ __device__ __forceinline__ float apply_epilogue(float x, const mggcn_epilogue &e
 // One group of LANES threads per item; NCH vectors of VEC floats per lane; the group covers
 // LANES*NCH*VEC features per pass and loops over passes when F is wider.
 // EXACT: F is a multiple of the pass width, so no per-lane column predicate is needed.
-template <int LANES, int NCH, int VEC, int UNROLL, bool EXACT>
+template <int LANES, int NCH, int VEC, int UNROLL, bool EXACT, bool GATHER = false>
 __global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
     constexpr int GROUPS = 32 / LANES;
     constexpr int TILE_F = LANES * NCH * VEC;
@@ -211,9 +250,11 @@ __global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
             for (int e = 0; e < VEC; ++e) acc[k][e] = 0.f;
         }
         const float *Bl = a.B + f0 + VEC * sl;
+        const float *Bown = GATHER ? a.g.B_own + f0 + VEC * sl : nullptr;
 
-        uint32_t c_cur = 0, c_nxt = 0;
+        uint32_t c_cur = GATHER ? a.g.own_lo : 0, c_nxt = 0;
         float v_cur = 0.f, v_nxt = 0.f;
+        int ready = 0;  // stages [0, ready] are known to be in place
         if ((uint32_t)sl < len) {
             c_cur = ldg_stream_u32(ci + sl, pol_s);
             v_cur = ldg_stream_f32(va + sl, pol_s);
@@ -224,7 +265,21 @@ __global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
                 c_nxt = ldg_stream_u32(ci + npos + sl, pol_s);
                 v_nxt = ldg_stream_f32(va + npos + sl, pol_s);
             } else {
-                c_nxt = 0; v_nxt = 0.f;
+                c_nxt = GATHER ? a.g.own_lo : 0; v_nxt = 0.f;
+            }
+            if (GATHER) {
+                // rows are stored in stage order, so the stage of a chunk only grows: wait (once) for the
+                // latest stage any lane of the warp is about to gather from
+                int blk = 0;
+#pragma unroll
+                for (int i = 1; i < 16; ++i) blk += c_cur >= a.g.cuts[i];
+                int st = blk - a.g.rank;
+                st += st < 0 ? a.g.P : 0;
+                const int smax = __reduce_max_sync(0xffffffffu, st);
+                if (smax > ready) {
+                    wait_stage(a.g.flags + smax, a.g.err);
+                    ready = smax;
+                }
             }
             const int rem = (int)len - (int)pos;  // entries of this group's item left (may be <= 0)
             const bool full = __all_sync(0xffffffffu, rem >= LANES);
@@ -236,10 +291,12 @@ __global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
                     for (int u = 0; u < UNROLL && u < LANES; ++u) {
                         const uint32_t c = __shfl_sync(0xffffffffu, c_cur, j + u, LANES);
                         const float *bp = Bl + (int64_t)c * a.ldb;
+                        if (GATHER && c - a.g.own_lo < a.g.own_n) bp = Bown + (int64_t)(c - a.g.own_lo) * a.ldb;
 #pragma unroll
                         for (int k = 0; k < NCH; ++k) {
                             if (EXACT || colok[k]) {
-                                b[u][k].load(bp + VEC * LANES * k, pol_b);
+                                if (GATHER) b[u][k].load_coherent(bp + VEC * LANES * k, pol_b);
+                                else b[u][k].load(bp + VEC * LANES * k, pol_b);
                             } else {
 #pragma unroll
                                 for (int e = 0; e < VEC; ++e) b[u][k].v[e] = 0.f;
@@ -270,10 +327,12 @@ __global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
                         v[u] = __shfl_sync(0xffffffffu, v_cur, j + u, LANES);
                         const bool ok = j + u < rem;
                         const float *bp = Bl + (int64_t)c * a.ldb;
+                        if (GATHER && c - a.g.own_lo < a.g.own_n) bp = Bown + (int64_t)(c - a.g.own_lo) * a.ldb;
 #pragma unroll
                         for (int k = 0; k < NCH; ++k) {
                             if (ok && colok[k]) {
-                                b[u][k].load(bp + VEC * LANES * k, pol_b);
+                                if (GATHER) b[u][k].load_coherent(bp + VEC * LANES * k, pol_b);
+                                else b[u][k].load(bp + VEC * LANES * k, pol_b);
                             } else {
 #pragma unroll
                                 for (int e = 0; e < VEC; ++e) b[u][k].v[e] = 0.f;
@@ -369,12 +428,16 @@ int launch_cfg(cudaStream_t st, const spmm_args &a) {
     if (grid > 0x7fffffffll) return fail(MGGCN_E_UNSUPPORTED, "SpMM grid too large");
     constexpr int U4 = LANES < 4 ? LANES : 4;
     const bool exact = a.F % (LANES * NCH * VEC) == 0;
-    if (g_unroll >= 8 && LANES >= 8) {
-        if (exact) spmm_kernel<LANES, NCH, VEC, 8, true><<<(unsigned)grid, threads, 0, st>>>(a);
-        else spmm_kernel<LANES, NCH, VEC, 8, false><<<(unsigned)grid, threads, 0, st>>>(a);
+    const unsigned gr = (unsigned)grid;
+    if (a.g.flags) {  // gathered multi-GPU operand
+        if (exact) spmm_kernel<LANES, NCH, VEC, U4, true, true><<<gr, threads, 0, st>>>(a);
+        else spmm_kernel<LANES, NCH, VEC, U4, false, true><<<gr, threads, 0, st>>>(a);
+    } else if (g_unroll >= 8 && LANES >= 8) {
+        if (exact) spmm_kernel<LANES, NCH, VEC, 8, true><<<gr, threads, 0, st>>>(a);
+        else spmm_kernel<LANES, NCH, VEC, 8, false><<<gr, threads, 0, st>>>(a);
     } else {
-        if (exact) spmm_kernel<LANES, NCH, VEC, U4, true><<<(unsigned)grid, threads, 0, st>>>(a);
-        else spmm_kernel<LANES, NCH, VEC, U4, false><<<(unsigned)grid, threads, 0, st>>>(a);
+        if (exact) spmm_kernel<LANES, NCH, VEC, U4, true><<<gr, threads, 0, st>>>(a);
+        else spmm_kernel<LANES, NCH, VEC, U4, false><<<gr, threads, 0, st>>>(a);
     }
     MGGCN_LAUNCH_CHECK();
     return MGGCN_OK;
@@ -383,7 +446,7 @@ int launch_cfg(cudaStream_t st, const spmm_args &a) {
 int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowptr, int rowptr64,
                   const uint32_t *colidx, const float *vals, const float *B, int64_t ldb, float *C,
                   int64_t ldc, int F, float alpha, float beta, const mggcn_epilogue *epi,
-                  const mggcn_spmm_plan_t *plan, void *ws) {
+                  const mggcn_spmm_plan_t *plan, void *ws, const mggcn::spmm_gather *gather = nullptr) {
     if (rows < 0 || cols < 0 || F < 0) return fail(MGGCN_E_INVALID, "negative dimension");
     if (rows == 0 || F == 0) return MGGCN_OK;
     if (!rowptr && !plan) return fail(MGGCN_E_INVALID, "rowptr is null");
@@ -408,6 +471,11 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
     a.alpha = alpha;
     a.beta = beta;
     a.policy = g_policy;
+    if (gather) {
+        if (!gather->flags || !gather->B_own || gather->P < 1 || gather->P > 16 || gather->rank < 0 || gather->rank >= gather->P)
+            return fail(MGGCN_E_INVALID, "bad gathered-operand description");
+        a.g = *gather;
+    }
     if (epi) a.epi = *epi;
     else memset(&a.epi, 0, sizeof a.epi);
     if (a.epi.kind == MGGCN_EPI_LEAKY_RELU_BWD && !a.epi.aux)
@@ -419,6 +487,7 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
 
     const bool aligned = ldb % 4 == 0 && ldc % 4 == 0 && ldb >= 4 * (int64_t)F4 &&
                          (reinterpret_cast<uintptr_t>(B) & 15) == 0 &&
+                         (!gather || (reinterpret_cast<uintptr_t>(gather->B_own) & 15) == 0) &&
                          (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
                          (reinterpret_cast<uintptr_t>(ws) & 15) == 0;
     int rc;
@@ -521,7 +590,35 @@ int plan_create(int64_t rows, const idx_t *rowptr, int split_nnz, mggcn_spmm_pla
 
 }  // namespace
 
+namespace mggcn {
+// engine.cu: the staged exchange folded into one launch
+int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx,
+                  const float *vals, const float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
+                  float beta, const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws, const spmm_gather &g) {
+    return spmm_dispatch(st, rows, cols, rowptr, 0, colidx, vals, gathered, ld, C, ldc, F, alpha, beta, epi, plan, ws, &g);
+}
+}  // namespace mggcn
+
 extern "C" {
+
+int mggcn_spmm_gathered_f32_i32(mggcn_stream_t stream, int64_t rows, int64_t cols, const uint32_t *rowptr,
+                                const uint32_t *colidx, const float *vals, const float *gathered, const float *B_own,
+                                int64_t ld, float *C, int64_t ldc, int F, float alpha, float beta, int P, int rank,
+                                const uint32_t *cuts, const uint32_t *stage_flags, int *err,
+                                const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws) {
+    if (!cuts || P < 1 || P > 16 || rank < 0 || rank >= P) return fail(MGGCN_E_INVALID, "bad partition description");
+    mggcn::spmm_gather g;
+    g.flags = stage_flags;
+    g.B_own = B_own;
+    g.own_lo = cuts[rank];
+    g.own_n = cuts[rank + 1] - cuts[rank];
+    g.P = P;
+    g.rank = rank;
+    g.err = err;
+    for (int i = 0; i < 16; ++i) g.cuts[i] = i < P ? cuts[i] : 0xFFFFFFFFu;
+    return spmm_dispatch(static_cast<cudaStream_t>(stream), rows, cols, rowptr, 0, colidx, vals, gathered, ld, C, ldc, F,
+                         alpha, beta, epi, plan, ws, &g);
+}
 
 int mggcn_spmm_csr_f32_i32(mggcn_stream_t stream, int64_t rows, int64_t cols, const uint32_t *rowptr,
                            const uint32_t *colidx, const float *vals, const float *B, int64_t ldb,

@@ -220,3 +220,62 @@ def test_full_size_properties_reddit_shape(mg, orc, cuda):
     ref = orc.spmm(srp, sci, sva, x.cpu().numpy(), acc64=True)
     got = Cx.cpu().numpy()[rows]
     assert float(np.abs(got - ref).max()) <= 1e-5
+
+
+@pytest.mark.parametrize("F,late", [(128, False), (128, True), (44, False), (256, True)])
+@pytest.mark.parametrize("P,rank", [(4, 1), (8, 7), (2, 0)])
+def test_gathered_block_row_matches_oracle(mg, orc, cuda, F, late, P, rank):
+    """mggcn_spmm_gathered_f32_i32: one launch over a rank's whole block row with rows stored in stage order and
+    global column ids (what the p2p engine runs per aggregation).  Own rows must come from B_own (their copy in
+    the gather buffer is poisoned), every other block from the gather buffer; with `late` the stage flags are
+    raised by another stream while the kernel is already running, so the kernel has to wait for them."""
+    import ctypes as C
+    torch = cuda
+    rng = np.random.default_rng(5)
+    n, deg = 4096, 40
+    rp, ci, va = random_csr(rng, n, n, deg, heavy=3)
+    cuts = mg.row_cuts(n, P)
+    r0, r1 = int(cuts[rank]), int(cuts[rank + 1])
+    # block row in stage order: own block first, then blocks rank+1, ... cyclically
+    frp = [0]
+    fci, fva = [], []
+    for r in range(r0, r1):
+        c, v = ci[int(rp[r]):int(rp[r + 1])], va[int(rp[r]):int(rp[r + 1])]
+        blk = np.searchsorted(cuts, c, side="right") - 1
+        stage = (blk - rank) % P
+        order = np.argsort(stage, kind="stable")
+        fci.append(c[order]); fva.append(v[order])
+        frp.append(frp[-1] + len(c))
+    frp = np.array(frp, np.uint64)
+    fci = np.concatenate(fci).astype(np.uint32); fva = np.concatenate(fva).astype(np.float32)
+    ld = (F + 3) // 4 * 4
+    B = rng.standard_normal((n, ld)).astype(np.float32)
+    want = orc.spmm(rp[r0:r1 + 1] - rp[r0], ci[int(rp[r0]):int(rp[r1])], va[int(rp[r0]):int(rp[r1])], B[:, :F], acc64=True)
+    scale = np.abs(orc.spmm(rp[r0:r1 + 1] - rp[r0], ci[int(rp[r0]):int(rp[r1])], np.abs(va[int(rp[r0]):int(rp[r1])]),
+                            np.abs(B[:, :F]), acc64=True)).max(axis=1)
+    gathered = torch.from_numpy(B).cuda()
+    own = gathered[r0:r1].clone()
+    gathered[r0:r1] = float("nan")
+    rpt, cit, vat = to_dev(torch, frp, fci, fva)
+    plan = mg.SpmmPlan(frp.astype(np.uint32), split_nnz=512)
+    ws = plan.workspace(F)
+    Cm = torch.full((r1 - r0, ld), 7.0, device="cuda")
+    flags = torch.zeros(16, dtype=torch.int32, device="cuda") if late else torch.ones(16, dtype=torch.int32, device="cuda")
+    err = torch.zeros(4, dtype=torch.int32, device="cuda")
+    cuts_h = np.ascontiguousarray(cuts, np.uint32)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    main = torch.cuda.current_stream()
+    if late:
+        with torch.cuda.stream(side):
+            torch.cuda._sleep(20_000_000)   # ~10 ms: the kernel below is resident and waiting by then
+            flags.fill_(1)
+    mg.check(mg.lib().mggcn_spmm_gathered_f32_i32(
+        C.c_void_p(main.cuda_stream), r1 - r0, n, rpt.data_ptr(), cit.data_ptr(), vat.data_ptr(), gathered.data_ptr(),
+        own.data_ptr(), ld, Cm.data_ptr(), ld, F, 1.0, 0.0, P, rank, cuts_h.ctypes.data, flags.data_ptr(), err.data_ptr(),
+        None, plan.handle, ws.data_ptr() if ws is not None else None))
+    torch.cuda.synchronize()
+    assert int(err[0]) == 0
+    got = Cm.cpu().numpy()[:, :F]
+    assert np.isfinite(got).all()
+    check(got, want, scale)
