@@ -28,6 +28,27 @@ from __graft_entry__ import load_package  # noqa: E402
 
 ADAM = dict(lr=1e-2, beta1=0.9, beta2=0.999, wd=5e-4, eps=1e-8)  # src/main.cpp:126,163
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """Libraries print banners on fd 1 (NCCL's version line, torchrun's notes): keep the real stdout for the ONE
+    JSON line and send everything else to stderr."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, line)
+
 
 def parse():
     ap = argparse.ArgumentParser()
@@ -44,6 +65,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=float, default=1.0, help="row fraction timed on the host cores")
     ap.add_argument("--cpu-repeats", type=int, default=3)
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--tune", nargs="*", default=[], help="key=value kernel knobs (mggcn_tune), experiments only")
     return ap.parse_args()
 
 
@@ -212,7 +234,7 @@ def run_reference(args, mg, rank):
                              "reference_detail": {"cmd": " ".join(cmd[1:]), "median_ms": float(np.median(times)) * 1e3,
                                                   "min_ms": float(np.min(times)) * 1e3, "losses": [l for (_, l, _, _) in ep][:12],
                                                   "wall_s": wall}})
-                print(json.dumps(base), flush=True)
+                emit(base)
                 return
             base["reference_binary_failed"] = (r.stderr or r.stdout)[-400:]
     # fallback: oracle port on the host cores
@@ -221,12 +243,13 @@ def run_reference(args, mg, rank):
     cb = cpu_epoch_sample(mg, A, A_T, X, sizes, args.cpu_sample, args.cpu_repeats)
     base.update({"value": cb["value"], "ms_per_step": cb["value"], "cpu_baseline": cb,
                  "e2e": {"value": cb["value"], "unit": "ms/epoch", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
-    print(json.dumps(base), flush=True)
+    emit(base)
 
 
 # ------------------------------------------------------------------------------------------------
 def main():
     args = parse()
+    claim_stdout()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -237,6 +260,9 @@ def main():
     if args.impl == "reference":
         run_reference(args, mg, rank)
         return
+    for kv in args.tune:
+        k, v = kv.split("=")
+        mg.lib().mggcn_tune(k.encode(), int(v))
     import torch
     import torch.distributed as dist
     assert torch.cuda.is_available(), "bench.py needs a GPU: the product has no CPU fallback"
@@ -388,7 +414,7 @@ def main():
                                f"{len(args.hidden)}x{args.hidden[0]} hidden, {C} classes (padded to {sizes[-1]})",
                    "P": P, "partition": "1-D row blocks, replicated weights", "comm": args.comm if P > 1 else "none",
                    "graph": not args.no_graph, "l2": "inputs larger than L2 (CSR 0.9 GB per operand, X 0.57 GB)",
-                   "scale": args.scale},
+                   "scale": args.scale, **({"tune": args.tune} if args.tune else {})},
         "e2e": {"value": e2e_wall, "unit": "ms/epoch", "device_ms": e2e_dev,
                 "h2d_bytes_per_step": int(N * X.shape[1] * 4 + N * 4), "d2h_bytes_per_step": 16 * P},
         "gpu_launches": int(launches),
@@ -410,7 +436,7 @@ def main():
     }
     if cpu:
         out["cpu_baseline"] = cpu
-    print(json.dumps(out), flush=True)
+    emit(out)
     eng.close()
     if P > 1:
         dist.destroy_process_group()

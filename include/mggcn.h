@@ -106,11 +106,13 @@ MGGCN_API int mggcn_spmm_csr_f32_i64(mggcn_stream_t stream, int64_t rows, int64_
  *  gathered: cols x F (leading dimension ld), global row order, filled block by block by copy engines /
  *     peers while the kernel runs; stage_flags[s] (s = 1..P-1, device memory) becomes non-zero after the
  *     block of stage s = block (rank+s)%P is complete.  B_own: this rank's own rows (same ld), complete
- *     at launch.  cuts: P+1 row cuts of the partition (host memory).  err (device, nullable) is raised
- *     to 2 if a flag does not arrive within ~4 s of SM clock -- the launch never hangs. */
+ *     at launch; they are copied into their place of `gathered` on `stream` ahead of the kernel (so
+ *     `gathered` is written by this call; pass NULL when they are there already).  cuts: P+1 row
+ *     cuts of the partition (host memory).  err (device, nullable) is raised to 2 if a flag does
+ *     not arrive within ~4 s of SM clock -- the launch never hangs. */
 MGGCN_API int mggcn_spmm_gathered_f32_i32(mggcn_stream_t stream, int64_t rows, int64_t cols,
                                           const uint32_t *rowptr, const uint32_t *colidx,
-                                          const float *vals, const float *gathered,
+                                          const float *vals, float *gathered,
                                           const float *B_own, int64_t ld, float *C, int64_t ldc, int F,
                                           float alpha, float beta, int P, int rank,
                                           const uint32_t *cuts, const uint32_t *stage_flags, int *err,

@@ -32,8 +32,10 @@ static inline double u01(uint64_t h) { return (double)(h >> 11) * (1.0 / 9007199
 // mggcn_spmm_gathered_f32_i32): see spmm_args::g.
 struct spmm_gather {
     const uint32_t *flags = nullptr;  // P words; flags[s] != 0: the block of stage s is in place (flags[0] unused)
-    const float *B_own = nullptr;     // this rank's own rows (stage 0), leading dimension = ldb
+    const float *B_own = nullptr;     // this rank's own rows (stage 0), leading dimension = ldb; copied into the
+                                      // gather buffer ahead of the launch (null: they are there already)
     uint32_t own_lo = 0, own_n = 0;   // global column range of the own rows
+    uint32_t ncols = 0;               // columns of the gathered operand (set by the dispatcher)
     int P = 1, rank = 0;
     int *err = nullptr;               // raised to 2 when a stage flag never arrives
     uint32_t cuts[16] = {0};          // cuts[i] = first global column of block i (i < P), 0xFFFFFFFF beyond

@@ -31,7 +31,7 @@ using namespace mggcn;
 
 namespace mggcn {
 int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx,
-                  const float *vals, const float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
+                  const float *vals, float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
                   float beta, const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws, const spmm_gather &g);
 }
 
@@ -391,22 +391,23 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
     }
     const size_t off = (size_t)(reinterpret_cast<const char *>(B) - e->arena);
     if (e->fused) {
-        // compute stream: clear the stage flags; exchange stream: barrier (every rank's B is complete), then
-        // pull block (rank+s)%P into its place of the all-gather buffer and publish flag s behind it.  The
-        // aggregation is ONE launch, issued as soon as the barrier has passed: it starts on the own block and
-        // waits on the device for a stage only if its block has not landed yet.
+        // compute stream: clear the stage flags, multiply the own block (no peer data needed) -- meanwhile the
+        // exchange stream passes the barrier (every rank's B is complete), pulls block (rank+s)%P into its place of
+        // the all-gather buffer and publishes flag s behind it.  The remote part of the block row is ONE launch,
+        // issued once the barrier has passed: it waits on the device for a stage only if its block has not landed.
         const adj_block &a = e->adj[which][0];
+        const adj_block &own = e->adj[which][1];
         int t_all, t_x;
         MGGCN_CUDA_TRY(cudaMemsetAsync(e->stage_flags, 0, 16 * sizeof(uint32_t), e->sc));
         MGGCN_CUDA_TRY(cudaEventRecord(e->ev_ready, e->sc));
         if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sm, e->ev_ready, 0));
         TRY(xbarrier(e, e->sm));
-        if (e->sm != e->sc) {
-            // the barrier kernel must not queue behind a grid of waiting CTAs: the SpMM starts after it
-            MGGCN_CUDA_TRY(cudaEventRecord(e->ev_bar, e->sm));
-            MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_bar, 0));
-        }
+        if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaEventRecord(e->ev_bar, e->sm));
         TRY(timer_begin(e, tname + "matmul-spmm", e->sc, &t_all));
+        TRY(mggcn_spmm_csr_f32_i32(e->sc, own.rows, own.cols, own.rowptr, own.colidx, own.vals, B, ld, C, ld, (int)F, 1.f,
+                                   0.f, nullptr, own.plan, e->ws_spmm));
+        // the barrier kernel must not queue behind a grid of waiting CTAs: the gathered launch starts after it
+        if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_bar, 0));
         bool sm_copies = false;
         for (int s = 1; s < P; ++s) {
             const int blk = (e->rank + s) % P;
@@ -436,14 +437,14 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
         }
         spmm_gather g;
         g.flags = e->stage_flags;
-        g.B_own = B;
+        g.B_own = nullptr;  // the own block has been multiplied already: the rows hold remote columns only
         g.own_lo = e->cuts[e->rank];
         g.own_n = e->cuts[e->rank + 1] - e->cuts[e->rank];
         g.P = P;
         g.rank = e->rank;
         g.err = e->dev_err;
         for (int i = 0; i < 16; ++i) g.cuts[i] = i < P ? e->cuts[i] : 0xFFFFFFFFu;
-        TRY(spmm_gathered(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, e->gather, ld, C, ld, (int)F, 1.f, 0.f, epi,
+        TRY(spmm_gathered(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, e->gather, ld, C, ld, (int)F, 1.f, 1.f, epi,
                           a.plan, e->ws_spmm, g));
         TRY(timer_end(e, e->sc, t_all));
         // nobody may overwrite B before every peer has pulled it
@@ -875,8 +876,9 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
     TRY(set_dev(e));
     size_t ws = e->ws_spmm_bytes;
     if (e->fused) {
-        // one CSR over this rank's whole block row: global column ids, every row in stage order
-        // (own block, then blocks rank+1, rank+2, ... cyclically), so one launch can follow the transfers
+        // slot 0: one CSR over the REMOTE part of this rank's block row: global column ids, every row in stage
+        // order (blocks rank+1, rank+2, ... cyclically), so one launch can follow the transfers; slot 1 (below):
+        // the own block with block-local columns, multiplied first while the barrier and the first transfer run
         adj_block &a = e->adj[which][0];
         if (a.plan) { mggcn_spmm_plan_destroy(a.plan); a.plan = nullptr; }
         if (a.rowptr) { cudaFree(a.rowptr); a.rowptr = nullptr; }
@@ -887,7 +889,8 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
         std::vector<uint64_t> rp((size_t)n + 1, 0);
         for (int64_t r = 0; r < n; ++r) {
             uint64_t c = 0;
-            for (int j = 0; j < P; ++j) c += blk_rowptr[j][r + 1] - blk_rowptr[j][r];
+            for (int j = 0; j < P; ++j)
+                if (j != e->rank) c += blk_rowptr[j][r + 1] - blk_rowptr[j][r];
             rp[(size_t)r + 1] = rp[(size_t)r] + c;
         }
         const uint64_t nnz = rp[(size_t)n];
@@ -897,7 +900,7 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
 #pragma omp parallel for schedule(static)
         for (int64_t r = 0; r < n; ++r) {
             uint64_t o = rp[(size_t)r];
-            for (int st = 0; st < P; ++st) {
+            for (int st = 1; st < P; ++st) {
                 const int j = (e->rank + st) % P;
                 const uint32_t base = e->cuts[j];
                 for (uint64_t k = blk_rowptr[j][r]; k < blk_rowptr[j][r + 1]; ++k, ++o) {
@@ -920,8 +923,9 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
         TRY(mggcn_spmm_plan_create_i32(a.rows, rp32.data(), 0, &a.plan));
         ws = std::max(ws, mggcn_spmm_plan_workspace_bytes(a.plan, (int)e->maxw));
     }
-    for (int j = 0; j < e->P && !e->fused; ++j) {
-        adj_block &a = e->adj[which][j];
+    for (int j = 0; j < e->P; ++j) {
+        if (e->fused && j != e->rank) continue;
+        adj_block &a = e->adj[which][e->fused ? 1 : j];
         if (a.plan) { mggcn_spmm_plan_destroy(a.plan); a.plan = nullptr; }
         if (a.rowptr) { cudaFree(a.rowptr); a.rowptr = nullptr; }
         if (a.colidx) { cudaFree(a.colidx); a.colidx = nullptr; }
@@ -1019,6 +1023,9 @@ int mggcn_engine_comm_connect(mggcn_engine_t *e, const void *handles, size_t len
         memcpy(&ptr, hs + (size_t)r * need + 8, 8);
         if (pid == (int64_t)getpid()) {
             // same process (the mg_gcn CLI drives all GPUs from one process): plain peer access
+            if (e->fused)
+                return fail(MGGCN_E_UNSUPPORTED, "MGGCN_COMM_P2P (one gathered launch per aggregation) needs one process per GPU: "
+                                                 "engines that share a process use MGGCN_COMM_P2P_STAGED");
             cudaPointerAttributes attr;
             MGGCN_CUDA_TRY(cudaPointerGetAttributes(&attr, reinterpret_cast<void *>((uintptr_t)ptr)));
             cudaError_t pe = cudaDeviceEnablePeerAccess(attr.device, 0);

@@ -83,8 +83,9 @@ struct spmm_args {
     mggcn_epilogue epi;
     int policy;
     // "gathered" multi-GPU form (GATHER kernels only): B is the all-gather buffer in global row order that
-    // the copy engines are still filling while the kernel runs; columns in [own_lo, own_lo + own_n) are this
-    // rank's own rows and are read from B_own instead.  flags[s] != 0 once the block of stage s has landed.
+    // the copy engines are still filling while the kernel runs; this rank's own rows (columns
+    // [own_lo, own_lo + own_n)) are copied into it on the launching stream right before the kernel, so every
+    // gather is one address computation.  flags[s] != 0 once the block of stage s has landed.
     mggcn::spmm_gather g;
 };
 
@@ -250,11 +251,13 @@ __global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
             for (int e = 0; e < VEC; ++e) acc[k][e] = 0.f;
         }
         const float *Bl = a.B + f0 + VEC * sl;
-        const float *Bown = GATHER ? a.g.B_own + f0 + VEC * sl : nullptr;
 
         uint32_t c_cur = GATHER ? a.g.own_lo : 0, c_nxt = 0;
         float v_cur = 0.f, v_nxt = 0.f;
-        int ready = 0;  // stages [0, ready] are known to be in place
+        // GATHER: the blocks of stages [0, ready] are in place; they cover the cyclic column interval
+        // [own_lo, own_lo + g_len) of the gather buffer (own block first, then blocks rank+1, ... cyclically)
+        int ready = 0;
+        uint32_t g_len = GATHER ? a.g.own_n : 0;
         if ((uint32_t)sl < len) {
             c_cur = ldg_stream_u32(ci + sl, pol_s);
             v_cur = ldg_stream_f32(va + sl, pol_s);
@@ -268,17 +271,22 @@ __global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
                 c_nxt = GATHER ? a.g.own_lo : 0; v_nxt = 0.f;
             }
             if (GATHER) {
-                // rows are stored in stage order, so the stage of a chunk only grows: wait (once) for the
-                // latest stage any lane of the warp is about to gather from
-                int blk = 0;
+                // rows are stored in stage order, so the stage of a chunk only grows: wait (once per stage and
+                // warp) until every column this chunk gathers from lies inside the interval that has landed
+                uint32_t cyc = c_cur - a.g.own_lo;
+                if (c_cur < a.g.own_lo) cyc += a.g.ncols;
+                while (__any_sync(0xffffffffu, cyc >= g_len)) {
+                    if (++ready >= a.g.P) break;  // malformed input: columns outside every block
+                    wait_stage(a.g.flags + ready, a.g.err);
+                    int b = a.g.rank + ready;
+                    b -= b >= a.g.P ? a.g.P : 0;
+                    uint32_t lo = 0, hi = a.g.ncols;
 #pragma unroll
-                for (int i = 1; i < 16; ++i) blk += c_cur >= a.g.cuts[i];
-                int st = blk - a.g.rank;
-                st += st < 0 ? a.g.P : 0;
-                const int smax = __reduce_max_sync(0xffffffffu, st);
-                if (smax > ready) {
-                    wait_stage(a.g.flags + smax, a.g.err);
-                    ready = smax;
+                    for (int i = 0; i < 16; ++i) {
+                        if (i == b) lo = a.g.cuts[i];
+                        if (i == b + 1 && i < a.g.P) hi = a.g.cuts[i];
+                    }
+                    g_len += hi - lo;
                 }
             }
             const int rem = (int)len - (int)pos;  // entries of this group's item left (may be <= 0)
@@ -291,7 +299,6 @@ __global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
                     for (int u = 0; u < UNROLL && u < LANES; ++u) {
                         const uint32_t c = __shfl_sync(0xffffffffu, c_cur, j + u, LANES);
                         const float *bp = Bl + (int64_t)c * a.ldb;
-                        if (GATHER && c - a.g.own_lo < a.g.own_n) bp = Bown + (int64_t)(c - a.g.own_lo) * a.ldb;
 #pragma unroll
                         for (int k = 0; k < NCH; ++k) {
                             if (EXACT || colok[k]) {
@@ -327,7 +334,6 @@ __global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
                         v[u] = __shfl_sync(0xffffffffu, v_cur, j + u, LANES);
                         const bool ok = j + u < rem;
                         const float *bp = Bl + (int64_t)c * a.ldb;
-                        if (GATHER && c - a.g.own_lo < a.g.own_n) bp = Bown + (int64_t)(c - a.g.own_lo) * a.ldb;
 #pragma unroll
                         for (int k = 0; k < NCH; ++k) {
                             if (ok && colok[k]) {
@@ -472,9 +478,17 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
     a.beta = beta;
     a.policy = g_policy;
     if (gather) {
-        if (!gather->flags || !gather->B_own || gather->P < 1 || gather->P > 16 || gather->rank < 0 || gather->rank >= gather->P)
+        if (!gather->flags || gather->P < 1 || gather->P > 16 || gather->rank < 0 || gather->rank >= gather->P)
             return fail(MGGCN_E_INVALID, "bad gathered-operand description");
+        if ((uint64_t)gather->own_lo + gather->own_n > (uint64_t)cols || cols > 0xFFFFFFFFll)
+            return fail(MGGCN_E_INVALID, "own column range outside the gathered operand");
         a.g = *gather;
+        a.g.ncols = (uint32_t)cols;
+        // the own block (stage 0) goes into its place of the gather buffer on this stream, ahead of the kernel
+        float *slot = const_cast<float *>(B) + (size_t)gather->own_lo * (size_t)ldb;
+        if (gather->B_own && gather->B_own != slot && gather->own_n > 0)
+            MGGCN_CUDA_TRY(cudaMemcpyAsync(slot, gather->B_own, (size_t)gather->own_n * (size_t)ldb * sizeof(float),
+                                           cudaMemcpyDeviceToDevice, st));
     }
     if (epi) a.epi = *epi;
     else memset(&a.epi, 0, sizeof a.epi);
@@ -593,7 +607,7 @@ int plan_create(int64_t rows, const idx_t *rowptr, int split_nnz, mggcn_spmm_pla
 namespace mggcn {
 // engine.cu: the staged exchange folded into one launch
 int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx,
-                  const float *vals, const float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
+                  const float *vals, float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
                   float beta, const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws, const spmm_gather &g) {
     return spmm_dispatch(st, rows, cols, rowptr, 0, colidx, vals, gathered, ld, C, ldc, F, alpha, beta, epi, plan, ws, &g);
 }
@@ -602,7 +616,7 @@ int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *r
 extern "C" {
 
 int mggcn_spmm_gathered_f32_i32(mggcn_stream_t stream, int64_t rows, int64_t cols, const uint32_t *rowptr,
-                                const uint32_t *colidx, const float *vals, const float *gathered, const float *B_own,
+                                const uint32_t *colidx, const float *vals, float *gathered, const float *B_own,
                                 int64_t ld, float *C, int64_t ldc, int F, float alpha, float beta, int P, int rank,
                                 const uint32_t *cuts, const uint32_t *stage_flags, int *err,
                                 const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws) {

@@ -31,7 +31,7 @@ def main():
     A, X, Y, C = mg.generate("oracle4k", seed=1)
     N = A.n
     sizes = [X.shape[1]] + args.hidden + [mg.pad_classes(C, world)]
-    comm = mg.COMM_P2P if args.comm == "p2p" else mg.COMM_NCCL
+    comm = {"p2p": mg.COMM_P2P, "p2p-staged": mg.COMM_P2P_STAGED, "nccl": mg.COMM_NCCL}[args.comm]
     nccl_id = None
     if comm == mg.COMM_NCCL:
         import ctypes
@@ -44,7 +44,7 @@ def main():
         nccl_id = bytes(idt.cpu().numpy().tobytes())
     eng, A_T = mg.build_rank_engine(A, sizes, world=world, rank=rank, device=local, use_graph=args.graph,
                                     nccl_id=nccl_id, comm=comm, overlap=not args.no_overlap)
-    if comm == mg.COMM_P2P:
+    if comm != mg.COMM_NCCL:
         ht = torch.frombuffer(bytearray(eng.comm_handle()), dtype=torch.uint8).cuda()
         allh = [torch.empty_like(ht) for _ in range(world)]
         dist.all_gather(allh, ht)

@@ -26,6 +26,61 @@ def timeit(fn, iters=5, warm=2):
     return float(np.median(ts)), float(np.min(ts))
 
 
+def gathered_bench(mg, AT, args):
+    """Kernel cost of the gathered form without any transfer: rank 0's block row (for rank 0 the stage order is
+    the column order, so the rows are used as they are), every stage flag already raised."""
+    import ctypes as C
+    P = args.gathered
+    n = AT.n
+    cuts = mg.row_cuts(n, P)
+    r1 = int(cuts[1])
+    e = int(AT.rowptr[r1])
+    rp = AT.rowptr[:r1 + 1].astype(np.uint32)
+    rpt = torch.from_numpy(rp.view(np.int32)).cuda()
+    cit = torch.from_numpy(AT.colidx[:e].view(np.int32)).cuda()
+    vat = torch.from_numpy(AT.vals[:e]).cuda()
+    plan = mg.SpmmPlan(rp)
+    blocks = AT.block_rows(cuts, cuts, only_row=0)
+    dev_blocks = []
+    for b in blocks:
+        brp = b.rowptr.astype(np.uint32)
+        dev_blocks.append((torch.from_numpy(brp.view(np.int32)).cuda(), torch.from_numpy(b.colidx.view(np.int32)).cuda(),
+                           torch.from_numpy(b.vals).cuda(), mg.SpmmPlan(brp), b.m))
+    flags = torch.ones(16, dtype=torch.int32, device="cuda")
+    err = torch.zeros(4, dtype=torch.int32, device="cuda")
+    cuts_h = np.ascontiguousarray(cuts, np.uint32)
+    st = torch.cuda.current_stream().cuda_stream
+    print(json.dumps({"gathered_P": P, "rows": r1, "cols": n, "nnz": e}), flush=True)
+    for F in args.F:
+        ld = (F + 3) // 4 * 4
+        B = (torch.rand((n, ld), device="cuda") * 2 - 1)
+        own = B[:r1].clone()
+        Cm = torch.empty((r1, ld), device="cuda")
+        Cs = torch.empty((r1, ld), device="cuda")
+        ws = plan.workspace(F)
+
+        def gathered():
+            mg.check(mg.lib().mggcn_spmm_gathered_f32_i32(
+                C.c_void_p(st), r1, n, rpt.data_ptr(), cit.data_ptr(), vat.data_ptr(), B.data_ptr(), own.data_ptr(), ld,
+                Cm.data_ptr(), ld, F, 1.0, 0.0, P, 0, cuts_h.ctypes.data, flags.data_ptr(), err.data_ptr(), None,
+                plan.handle, ws.data_ptr() if ws is not None else None))
+
+        def plain():
+            mg.spmm(rpt, cit, vat, B, Cm, cols=n, F=F, plan=plan)
+
+        def staged():
+            for s, (a, b, c, pl, m) in enumerate(dev_blocks):
+                lo = int(cuts[s])
+                mg.spmm(a, b, c, B[lo:lo + m], Cs, cols=m, F=F, beta=0.0 if s == 0 else 1.0, plan=pl)
+        for tag, fn in (("gathered-1launch", gathered), ("plain-1launch-global-cols", plain),
+                        (f"staged-{P}launches", staged)):
+            med, mn = timeit(fn)
+            print(json.dumps({"tag": tag, "F": F, "ms_med": round(med, 4), "ms_min": round(mn, 4),
+                              "gather_GBps": round(e * F * 4 / mn / 1e6, 1)}), flush=True)
+        gathered(); staged()
+        print(json.dumps({"max_abs_diff_gathered_vs_staged": float((Cm - Cs).abs().max())}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--shape", default="reddit")
@@ -36,6 +91,8 @@ def main():
     ap.add_argument("--cusparse", action="store_true")
     ap.add_argument("--splits", type=int, nargs="*", default=[])
     ap.add_argument("--slices", type=int, nargs="*", default=[], help="feature-slice counts: k launches over F/k-wide column windows")
+    ap.add_argument("--gathered", type=int, default=0, help="P: time rank 0's block row as ONE gathered launch (flags preset), "
+                    "as one plain launch with global columns, and as P staged launches")
     ap.add_argument("--unroll", type=int, default=4)
     ap.add_argument("--threads", type=int, default=64)
     args = ap.parse_args()
@@ -44,6 +101,9 @@ def main():
     A, _, _, _ = mg.generate(args.shape, seed=1, features=False, scale=args.scale)
     A.normalize(True)
     AT = A.transpose()
+    if args.gathered > 1:
+        gathered_bench(mg, AT, args)
+        return
     if args.blocks > 1:
         cuts = mg.row_cuts(AT.n, args.blocks)
         AT = AT.block_rows(cuts, cuts, only_row=0)[0]
