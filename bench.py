@@ -58,7 +58,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--shape", default="reddit")
     ap.add_argument("--hidden", type=int, nargs="+", default=[128, 128, 128])
-    ap.add_argument("--comm", default="p2p", choices=["nccl", "p2p", "p2p-staged"])
+    ap.add_argument("--comm", default="p2p-staged", choices=["nccl", "p2p", "p2p-staged"],
+                    help="exchange back-end at N > 1: p2p-staged (measured fastest at 2/4/8 GPUs), p2p = gathered single launch, nccl")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the graph (debugging only; marks the line)")
@@ -371,7 +372,8 @@ def main():
         dom_ms = float(np.mean(dom)) if dom else float("nan")
         alg = spmm_alg_bytes(n_loc, N, dom_nnz, F)
         dom_name = (f"spmm_kernel<32,1,4> forward, F={F}, whole matrix" if P == 1 else
-                    f"spmm_kernel<32,1,4,gathered> forward, F={F}, block row {n_loc}x{N} in one launch (waits on-device for the peers' blocks)")
+                    f"spmm_kernel<32,1,4> own block + spmm_kernel<32,1,4,gathered> remote blocks, forward, F={F}, block row {n_loc}x{N} "
+                    "(the gathered launch waits on-device for the peers' blocks)")
     else:
         dom = [v for k, v in med.items() if k.endswith("_matmul-spmm-stage") and k.split("_")[1] == "0"
                and not k.startswith(f"{len(sizes) - 2}_")]

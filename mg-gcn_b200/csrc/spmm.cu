@@ -198,8 +198,8 @@ __device__ __forceinline__ float apply_epilogue(float x, const mggcn_epilogue &e
 // One group of LANES threads per item; NCH vectors of VEC floats per lane; the group covers
 // LANES*NCH*VEC features per pass and loops over passes when F is wider.
 // EXACT: F is a multiple of the pass width, so no per-lane column predicate is needed.
-template <int LANES, int NCH, int VEC, int UNROLL, bool EXACT, bool GATHER = false>
-__global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
+template <int LANES, int NCH, int VEC, int UNROLL, bool EXACT, bool GATHER>
+__device__ __forceinline__ void spmm_body(const spmm_args &a) {
     constexpr int GROUPS = 32 / LANES;
     constexpr int TILE_F = LANES * NCH * VEC;
     const int lane = threadIdx.x & 31;
@@ -405,6 +405,10 @@ __global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
     }
 }
 
+template <int LANES, int NCH, int VEC, int UNROLL, bool EXACT, bool GATHER = false>
+__global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
+    spmm_body<LANES, NCH, VEC, UNROLL, EXACT, GATHER>(a);
+}
 // Adds the partial sums of every split row in segment order and finishes the row.
 __global__ void spmm_fixup_kernel(const split_row *rows, int64_t n_split, const float *partial,
                                   int64_t ldp, float *C, int64_t ldc, int F, float alpha, float beta,

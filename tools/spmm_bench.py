@@ -93,10 +93,14 @@ def main():
     ap.add_argument("--slices", type=int, nargs="*", default=[], help="feature-slice counts: k launches over F/k-wide column windows")
     ap.add_argument("--gathered", type=int, default=0, help="P: time rank 0's block row as ONE gathered launch (flags preset), "
                     "as one plain launch with global columns, and as P staged launches")
+    ap.add_argument("--tune", nargs="*", default=[], help="key=value knobs passed to mggcn_tune")
     ap.add_argument("--unroll", type=int, default=4)
     ap.add_argument("--threads", type=int, default=64)
     args = ap.parse_args()
     mg = load_package()
+    for kv in args.tune:
+        k, v = kv.split("=")
+        mg.lib().mggcn_tune(k.encode(), int(v))
     t0 = time.time()
     A, _, _, _ = mg.generate(args.shape, seed=1, features=False, scale=args.scale)
     A.normalize(True)
