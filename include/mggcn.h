@@ -300,8 +300,12 @@ typedef struct {
  *        memory order the ranks; gradients are summed in rank order from the peers' arenas.  Needs
  *        mggcn_engine_comm_handle / mggcn_engine_comm_connect after create.
  *  P2P_STAGED: the same transfers with the reference's structure -- one SpMM launch per stage on a
- *        double-buffered staging area (src/cuda_utils.hpp:57-92). */
-enum { MGGCN_COMM_NCCL = 0, MGGCN_COMM_P2P = 1, MGGCN_COMM_P2P_STAGED = 2 };
+ *        double-buffered staging area (src/cuda_utils.hpp:57-92).
+ *  P2P_GROUPED: the transfers of P2P (all-gather buffer), multiplied by plain launches over groups of
+ *        stages -- own block | stage 1 | stages 2-3 | 4-7 | 8-15 -- each ordered behind the transfer of
+ *        its last block by a stream event: later launches see longer rows and bigger grids (which is what
+ *        small blocks lack) while the first ones start as early as the staged form does. */
+enum { MGGCN_COMM_NCCL = 0, MGGCN_COMM_P2P = 1, MGGCN_COMM_P2P_STAGED = 2, MGGCN_COMM_P2P_GROUPED = 3 };
 
 MGGCN_API int mggcn_nccl_unique_id(void *id128);
 MGGCN_API int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out);

@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libmggcn.so")
 INCLUDE = os.path.join(os.path.dirname(_HERE), "include", "mggcn.h")
 
 EPI_NONE, EPI_LEAKY_RELU, EPI_LEAKY_RELU_BWD = 0, 1, 2
-COMM_NCCL, COMM_P2P, COMM_P2P_STAGED = 0, 1, 2
+COMM_NCCL, COMM_P2P, COMM_P2P_STAGED, COMM_P2P_GROUPED = 0, 1, 2, 3
 
 
 class MggcnError(RuntimeError):

@@ -280,6 +280,10 @@ struct mggcn_engine {
     // gathered form (p2p back-end): one launch per aggregation over the whole block row; the copy engines
     // fill `gather` (all ranks' rows, global order) while the kernel already works on the stages that landed
     bool fused = false;
+    // grouped form: same all-gather buffer, but plain launches over GROUPS of stages -- own block | stage 1 |
+    // stages 2-3 | 4-7 | 8-15 -- each ordered behind the transfer of its last block with a stream event
+    bool grouped = false;
+    std::vector<std::pair<int, int>> groups;  // [first stage, end stage) per launch
     float *gather = nullptr;
     uint32_t *stage_flags = nullptr;
     cudaEvent_t ev_bar = nullptr, ev_copied = nullptr;
@@ -390,6 +394,52 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
         return MGGCN_OK;
     }
     const size_t off = (size_t)(reinterpret_cast<const char *>(B) - e->arena);
+    if (e->grouped) {
+        // exchange stream: barrier (every rank's B is complete), then pull block (rank+s)%P into its place of the
+        // all-gather buffer, s = 1..P-1, with an event behind the last block of every group.  Compute stream: the
+        // own block at once, then one plain launch per group of stages (global columns into the all-gather
+        // buffer) behind that group's event.
+        int t_all, t_x, t_s;
+        MGGCN_CUDA_TRY(cudaEventRecord(e->ev_ready, e->sc));
+        if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sm, e->ev_ready, 0));
+        TRY(xbarrier(e, e->sm));
+        TRY(timer_begin(e, tname + "matmul-spmm", e->sc, &t_all));
+        const int G = (int)e->groups.size();
+        for (int g = 0; g < G; ++g) {
+            const adj_block &a = e->adj[which][g];
+            for (int s = std::max(1, e->groups[g].first); s < e->groups[g].second; ++s) {
+                const int blk = (e->rank + s) % P;
+                const size_t count = ((size_t)e->cuts[blk + 1] - (size_t)e->cuts[blk]) * (size_t)ld;
+                float *dst = e->gather + (size_t)e->cuts[blk] * (size_t)ld;
+                TRY(timer_begin(e, tname + std::to_string(s) + "_matmul-bcast", e->sm, &t_x));
+                if (e->peer_inproc[blk] && !e->capturing) {
+                    pull_copy_kernel<<<64, 512, 0, e->sm>>>(reinterpret_cast<const float4 *>(e->peer_arena[blk] + off),
+                                                            reinterpret_cast<float4 *>(dst), count / 4);
+                    MGGCN_LAUNCH_CHECK();
+                } else {
+                    MGGCN_CUDA_TRY(cudaMemcpyAsync(dst, e->peer_arena[blk] + off, count * sizeof(float),
+                                                   cudaMemcpyDeviceToDevice, e->sm));
+                }
+                TRY(timer_end(e, e->sm, t_x));
+            }
+            if (g > 0 && e->sm != e->sc) {
+                MGGCN_CUDA_TRY(cudaEventRecord(e->ev_xfer[g], e->sm));
+                MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_xfer[g], 0));
+            }
+            TRY(timer_begin(e, tname + std::to_string(g) + "_matmul-spmm-stage", e->sc, &t_s));
+            TRY(mggcn_spmm_csr_f32_i32(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, g == 0 ? B : e->gather, ld, C, ld,
+                                       (int)F, 1.f, g == 0 ? 0.f : 1.f, g == G - 1 ? epi : nullptr, a.plan, e->ws_spmm));
+            TRY(timer_end(e, e->sc, t_s));
+        }
+        TRY(timer_end(e, e->sc, t_all));
+        // nobody may overwrite B before every peer has pulled it
+        TRY(xbarrier(e, e->sm));
+        if (e->sm != e->sc) {
+            MGGCN_CUDA_TRY(cudaEventRecord(e->ev_done, e->sm));
+            MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_done, 0));
+        }
+        return MGGCN_OK;
+    }
     if (e->fused) {
         // compute stream: clear the stage flags, multiply the own block (no peer data needed) -- meanwhile the
         // exchange stream passes the barrier (every rank's B is complete), pulls block (rank+s)%P into its place of
@@ -700,8 +750,14 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     e->overlap = cfg->overlap != 0;
     e->exact = cfg->exact_grads != 0;
     e->use_graph = cfg->use_graph != 0;
-    e->p2p = (cfg->comm_backend == MGGCN_COMM_P2P || cfg->comm_backend == MGGCN_COMM_P2P_STAGED) && cfg->world > 1;
+    e->p2p = (cfg->comm_backend == MGGCN_COMM_P2P || cfg->comm_backend == MGGCN_COMM_P2P_STAGED ||
+              cfg->comm_backend == MGGCN_COMM_P2P_GROUPED) && cfg->world > 1;
     e->fused = e->p2p && cfg->comm_backend == MGGCN_COMM_P2P && !getenv("MGGCN_STAGED");
+    e->grouped = e->p2p && cfg->comm_backend == MGGCN_COMM_P2P_GROUPED;
+    if (e->grouped) {
+        e->groups.push_back({0, 1});
+        for (int s0 = 1; s0 < e->P; s0 *= 2) e->groups.push_back({s0, std::min(2 * s0, e->P)});
+    }
     e->timers_on = cfg->timers != 0 && !e->use_graph;
     e->slope = cfg->lrelu_slope;
     e->N = cfg->n_global;
@@ -780,7 +836,7 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     need(n * (size_t)e->maxw * 4);                                 // HW
     need(n * (size_t)e->maxw * 4);                                 // G0
     need(n * (size_t)e->maxw * 4);                                 // G1
-    if (e->fused) {
+    if (e->fused || e->grouped) {
         need((size_t)e->N * (size_t)e->maxw * 4);
         need(64);
     } else if (e->P > 1) {
@@ -809,7 +865,7 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     e->HW = carve<float>(cur, n * (size_t)e->maxw);
     e->G[0] = carve<float>(cur, n * (size_t)e->maxw);
     e->G[1] = carve<float>(cur, n * (size_t)e->maxw);
-    if (e->fused) {
+    if (e->fused || e->grouped) {
         e->gather = carve<float>(cur, (size_t)e->N * (size_t)e->maxw);
         e->stage_flags = carve<uint32_t>(cur, 16);
     } else if (e->P > 1) {
@@ -875,11 +931,18 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
     if (!e || which < 0 || which > 1 || !blk_rowptr || !blk_colidx || !blk_vals) return fail(MGGCN_E_INVALID, "bad argument");
     TRY(set_dev(e));
     size_t ws = e->ws_spmm_bytes;
-    if (e->fused) {
-        // slot 0: one CSR over the REMOTE part of this rank's block row: global column ids, every row in stage
-        // order (blocks rank+1, rank+2, ... cyclically), so one launch can follow the transfers; slot 1 (below):
-        // the own block with block-local columns, multiplied first while the barrier and the first transfer run
-        adj_block &a = e->adj[which][0];
+    // merged CSRs over ranges of stages (global column ids into the all-gather buffer, every row in stage order:
+    // blocks rank+s0, rank+s0+1, ... cyclically).  Gathered form: slot 0 = all remote stages [1, P) in one CSR, so
+    // one launch can follow the transfers; slot 1 (below) = the own block with block-local columns, multiplied
+    // first while the barrier and the first transfer run.  Grouped form: slot g = stages of group g (g >= 1),
+    // slot 0 (below) = the own block.
+    std::vector<std::pair<int, std::pair<int, int>>> merged;  // (slot, [s0, s1))
+    if (e->fused) merged.push_back({0, {1, e->P}});
+    if (e->grouped)
+        for (size_t g = 1; g < e->groups.size(); ++g) merged.push_back({(int)g, e->groups[g]});
+    for (const auto &mg : merged) {
+        adj_block &a = e->adj[which][mg.first];
+        const int s0 = mg.second.first, s1 = mg.second.second;
         if (a.plan) { mggcn_spmm_plan_destroy(a.plan); a.plan = nullptr; }
         if (a.rowptr) { cudaFree(a.rowptr); a.rowptr = nullptr; }
         if (a.colidx) { cudaFree(a.colidx); a.colidx = nullptr; }
@@ -889,8 +952,10 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
         std::vector<uint64_t> rp((size_t)n + 1, 0);
         for (int64_t r = 0; r < n; ++r) {
             uint64_t c = 0;
-            for (int j = 0; j < P; ++j)
-                if (j != e->rank) c += blk_rowptr[j][r + 1] - blk_rowptr[j][r];
+            for (int st = s0; st < s1; ++st) {
+                const int j = (e->rank + st) % P;
+                c += blk_rowptr[j][r + 1] - blk_rowptr[j][r];
+            }
             rp[(size_t)r + 1] = rp[(size_t)r] + c;
         }
         const uint64_t nnz = rp[(size_t)n];
@@ -900,7 +965,7 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
 #pragma omp parallel for schedule(static)
         for (int64_t r = 0; r < n; ++r) {
             uint64_t o = rp[(size_t)r];
-            for (int st = 1; st < P; ++st) {
+            for (int st = s0; st < s1; ++st) {
                 const int j = (e->rank + st) % P;
                 const uint32_t base = e->cuts[j];
                 for (uint64_t k = blk_rowptr[j][r]; k < blk_rowptr[j][r + 1]; ++k, ++o) {
@@ -924,8 +989,8 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
         ws = std::max(ws, mggcn_spmm_plan_workspace_bytes(a.plan, (int)e->maxw));
     }
     for (int j = 0; j < e->P; ++j) {
-        if (e->fused && j != e->rank) continue;
-        adj_block &a = e->adj[which][e->fused ? 1 : j];
+        if ((e->fused || e->grouped) && j != e->rank) continue;
+        adj_block &a = e->adj[which][e->fused ? 1 : e->grouped ? 0 : j];
         if (a.plan) { mggcn_spmm_plan_destroy(a.plan); a.plan = nullptr; }
         if (a.rowptr) { cudaFree(a.rowptr); a.rowptr = nullptr; }
         if (a.colidx) { cudaFree(a.colidx); a.colidx = nullptr; }

@@ -31,7 +31,8 @@ def main():
     A, X, Y, C = mg.generate("oracle4k", seed=1)
     N = A.n
     sizes = [X.shape[1]] + args.hidden + [mg.pad_classes(C, world)]
-    comm = {"p2p": mg.COMM_P2P, "p2p-staged": mg.COMM_P2P_STAGED, "nccl": mg.COMM_NCCL}[args.comm]
+    comm = {"p2p": mg.COMM_P2P, "p2p-staged": mg.COMM_P2P_STAGED, "p2p-grouped": mg.COMM_P2P_GROUPED,
+            "nccl": mg.COMM_NCCL}[args.comm]
     nccl_id = None
     if comm == mg.COMM_NCCL:
         import ctypes

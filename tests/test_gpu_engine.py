@@ -150,7 +150,7 @@ def test_state_errors(mg, cuda):
 
 
 @pytest.mark.parametrize("comm,graph", [("nccl", False), ("p2p", False), ("p2p", True), ("nccl", True),
-                                        ("p2p-staged", False), ("p2p-staged", True)])
+                                        ("p2p-staged", False), ("p2p-staged", True), ("p2p-grouped", False), ("p2p-grouped", True)])
 def test_two_gpu_engine_matches_oracle(cuda, comm, graph):
     """One process per GPU (torchrun), world 2: staged exchange + SpMM, gradient reduction, Adam."""
     import os
