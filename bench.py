@@ -58,8 +58,9 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--shape", default="reddit")
     ap.add_argument("--hidden", type=int, nargs="+", default=[128, 128, 128])
-    ap.add_argument("--comm", default="p2p-staged", choices=["nccl", "p2p", "p2p-staged", "p2p-grouped"],
-                    help="exchange back-end at N > 1: p2p-staged (measured fastest at 2/4/8 GPUs), p2p = gathered single launch, nccl")
+    ap.add_argument("--comm", default="p2p-grouped", choices=["nccl", "p2p", "p2p-staged", "p2p-grouped"],
+                    help="exchange back-end at N > 1: p2p-grouped (measured fastest: 3.27 ms at 8 GPUs), p2p-staged (3.54), "
+                         "p2p = gathered single launch (3.75), nccl")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the graph (debugging only; marks the line)")

@@ -1,8 +1,8 @@
 // dist_gcn<true, x_t, v_t, r_t>: the multi-GPU model of src/gcn.hpp:997-1056 -- one engine per GPU,
 // all driven from this process (the reference is single-process too).  Included by gcn_model.hpp.
 //
-// Exchange back-end: peer memory, staged form (MGGCN_COMM_P2P_STAGED: one SpMM launch per stage, the
-// reference's structure).  The single-launch gathered form (MGGCN_COMM_P2P) is for one process per GPU: with
+// Exchange back-end: peer memory, grouped form (MGGCN_COMM_P2P_GROUPED: plain SpMM launches over groups of
+// stages, ordered behind the transfers with stream events).  The single-launch gathered form (MGGCN_COMM_P2P) is for one process per GPU: with
 // every engine in ONE process, peer copies between two devices of the same process queue behind kernels that
 // are still running on the other device, and a kernel that waits on the device for such a copy can stall until
 // the barrier timeout.  The engines are wired to each other in-process
@@ -70,7 +70,7 @@ class dist_gcn {
             cfg.use_graph = opt.use_graph && !opt.timers;
             cfg.timers = opt.timers;
             cfg.lrelu_slope = opt.lrelu_slope;
-            cfg.comm_backend = MGGCN_COMM_P2P_STAGED;
+            cfg.comm_backend = MGGCN_COMM_P2P_GROUPED;
             auto box = std::make_shared<detail::engine_box>();
             CHECK_MGGCN(mggcn_engine_create(&cfg, &box->e));
             std::vector<block_t> fwd, bwd;

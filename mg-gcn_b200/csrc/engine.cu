@@ -754,6 +754,13 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
               cfg->comm_backend == MGGCN_COMM_P2P_GROUPED) && cfg->world > 1;
     e->fused = e->p2p && cfg->comm_backend == MGGCN_COMM_P2P && !getenv("MGGCN_STAGED");
     e->grouped = e->p2p && cfg->comm_backend == MGGCN_COMM_P2P_GROUPED;
+    // the all-gather buffer holds every rank's rows at the widest layer: past 32 GB per rank (papers100M-shape:
+    // 57 GB) the grouped form falls back to the double-buffered staged exchange
+    if (e->grouped) {
+        int64_t w = 0;
+        for (int i = 0; i <= cfg->num_layers; ++i) w = std::max<int64_t>(w, cfg->sizes[i]);
+        if ((double)cfg->n_global * (double)w * 4.0 > 32.0 * (1ull << 30)) e->grouped = false;
+    }
     if (e->grouped) {
         e->groups.push_back({0, 1});
         for (int s0 = 1; s0 < e->P; s0 *= 2) e->groups.push_back({s0, std::min(2 * s0, e->P)});
