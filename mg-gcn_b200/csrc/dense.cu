@@ -267,33 +267,75 @@ int gemm_launch(cudaStream_t st, gemm_args &g, int nz) {
 }
 
 // ------------------------------------------------------------------------------------------------
-__global__ void colsum_stage1(const float *G, int64_t ldg, int64_t rows, int64_t N, int64_t rows_per_cta,
-                              float *part) {
-    __shared__ float red[8][33];
+// G_b = 1^T G (src/gcn.hpp:288-296 does it with a GEMV against a vector of ones).  Two deterministic levels:
+// a CTA of 32 x 8 threads owns rows_per_cta rows; thread (x, y) adds rows y, y+8, ... of a 128-bit column group
+// (four independent accumulator sets keep four loads in flight), the 8 row groups are added in y order;
+// stage 2 adds the per-CTA rows of `part` the same way (8 interleaved partial sums, then y order).
+template <bool VEC4>
+__global__ void __launch_bounds__(256) colsum_stage1(const float *G, int64_t ldg, int64_t rows, int64_t N,
+                                                     int64_t rows_per_cta, float *part) {
+    __shared__ float red[8][32][4 + 1];
+    const int tx = threadIdx.x, ty = threadIdx.y;
     const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
     const int64_t r1 = min(rows, r0 + rows_per_cta);
-    for (int64_t c0 = 0; c0 < N; c0 += 32) {
-        const int64_t col = c0 + threadIdx.x;
-        float s = 0.f;
-        if (col < N)
-            for (int64_t r = r0 + threadIdx.y; r < r1; r += 8) s += G[r * ldg + col];
-        red[threadIdx.y][threadIdx.x] = s;
-        __syncthreads();
-        if (threadIdx.y == 0 && col < N) {
-            float t = 0.f;
+    for (int64_t c0 = 0; c0 < N; c0 += 128) {
+        const int64_t col = c0 + 4 * tx;
+        float s[4][4];
 #pragma unroll
-            for (int y = 0; y < 8; ++y) t += red[y][threadIdx.x];
-            part[(int64_t)blockIdx.x * N + col] = t;
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) s[u][e] = 0.f;
+        if (col < N) {
+            int64_t r = r0 + ty;
+            if (VEC4 && col + 3 < N) {
+                for (; r + 24 < r1; r += 32) {
+                    float4 v[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const float4 *>(G + (r + 8 * u) * ldg + col);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { s[u][0] += v[u].x; s[u][1] += v[u].y; s[u][2] += v[u].z; s[u][3] += v[u].w; }
+                }
+                for (; r < r1; r += 8) {
+                    const float4 v = *reinterpret_cast<const float4 *>(G + r * ldg + col);
+                    s[0][0] += v.x; s[0][1] += v.y; s[0][2] += v.z; s[0][3] += v.w;
+                }
+            } else {
+                for (; r < r1; r += 8)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        if (col + e < N) s[0][e] += G[r * ldg + col + e];
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) red[ty][tx][e] = (s[0][e] + s[1][e]) + (s[2][e] + s[3][e]);
+        __syncthreads();
+        if (ty == 0 && col < N) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (col + e >= N) break;
+                float t = 0.f;
+#pragma unroll
+                for (int y = 0; y < 8; ++y) t += red[y][tx][e];
+                part[(int64_t)blockIdx.x * N + col + e] = t;
+            }
         }
         __syncthreads();
     }
 }
-__global__ void colsum_stage2(const float *part, int nparts, int64_t N, float *out) {
-    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (col >= N) return;
+__global__ void __launch_bounds__(256) colsum_stage2(const float *part, int nparts, int64_t N, float *out) {
+    __shared__ float red[8][33];
+    const int64_t col = (int64_t)blockIdx.x * 32 + threadIdx.x;
     float s = 0.f;
-    for (int p = 0; p < nparts; ++p) s += part[(int64_t)p * N + col];
-    out[col] = s;
+    if (col < N)
+        for (int p = threadIdx.y; p < nparts; p += 8) s += part[(int64_t)p * N + col];
+    red[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && col < N) {
+        float t = 0.f;
+#pragma unroll
+        for (int y = 0; y < 8; ++y) t += red[y][threadIdx.x];
+        out[col] = t;
+    }
 }
 int colsum_parts(int64_t rows) { return (int)std::max<int64_t>(1, std::min<int64_t>(148 * 4, (rows + 255) / 256)); }
 
@@ -473,9 +515,11 @@ int mggcn_colsum_f32(mggcn_stream_t stream, int64_t rows, int64_t N, const float
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int parts = colsum_parts(rows);
     const int64_t rpc = (rows + parts - 1) / parts;
-    colsum_stage1<<<parts, dim3(32, 8), 0, st>>>(G, ldg, rows, N, std::max<int64_t>(rpc, 1), static_cast<float *>(ws));
+    const bool vec4 = ldg % 4 == 0 && (reinterpret_cast<uintptr_t>(G) & 15) == 0;
+    if (vec4) colsum_stage1<true><<<parts, dim3(32, 8), 0, st>>>(G, ldg, rows, N, std::max<int64_t>(rpc, 1), static_cast<float *>(ws));
+    else colsum_stage1<false><<<parts, dim3(32, 8), 0, st>>>(G, ldg, rows, N, std::max<int64_t>(rpc, 1), static_cast<float *>(ws));
     MGGCN_LAUNCH_CHECK();
-    colsum_stage2<<<(unsigned)((N + 127) / 128), 128, 0, st>>>(static_cast<const float *>(ws), parts, N, out);
+    colsum_stage2<<<(unsigned)((N + 31) / 32), dim3(32, 8), 0, st>>>(static_cast<const float *>(ws), parts, N, out);
     MGGCN_LAUNCH_CHECK();
     return MGGCN_OK;
 }

@@ -194,6 +194,14 @@ int publish_flag(cudaStream_t st, uint32_t *flag, bool capturing) {
     return MGGCN_OK;
 }
 
+__global__ void pad_rows_kernel(const float *src, int64_t rows, int64_t cols, float *dst, int64_t ld) {
+    const int64_t total = rows * ld;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / ld, c = i - r * ld;
+        dst[i] = c < cols ? src[r * cols + c] : 0.f;
+    }
+}
+
 struct grad_peers {
     const float *g[kMaxRanks];
 };
@@ -244,6 +252,11 @@ struct layer_t {
     int64_t in = 0, out = 0;
     bool activation = false, gemm_first = false;
     float *W = nullptr, *b = nullptr, *GW = nullptr, *Gb = nullptr;  // views into the packed vectors
+    // the tensor-core GEMM reads W through TMA (16-byte aligned base and row pitch): when out % 4 != 0 (41
+    // classes) the forward pass refreshes a copy with rows padded to a multiple of 4 floats and the GEMMs of the
+    // epoch read that one; otherwise Wt == W
+    float *Wt = nullptr, *Wpad = nullptr;
+    int64_t ldw = 0;
     float *Z = nullptr;   // layer output, n x up4(out)
     float *AH = nullptr;  // exact_grads && !gemm_first: saved A*H, n x up4(in)
 };
@@ -578,6 +591,11 @@ int forward(eng *e) {
     for (int l = 0; l < e->L; ++l) {
         layer_t &y = e->layers[l];
         const std::string nm = std::to_string(l) + "_0_";
+        if (y.Wpad) {
+            const int64_t total = y.in * y.ldw;
+            pad_rows_kernel<<<(unsigned)std::min<int64_t>((total + 255) / 256, 148 * 4), 256, 0, e->sc>>>(y.W, y.in, y.out, y.Wpad, y.ldw);
+            MGGCN_LAUNCH_CHECK();
+        }
         mggcn_epilogue act{};
         act.kind = y.activation ? MGGCN_EPI_LEAKY_RELU : MGGCN_EPI_NONE;
         act.slope = e->slope;
@@ -586,7 +604,7 @@ int forward(eng *e) {
             mggcn_epilogue bias{};
             bias.bias = y.b;
             TRY(timer_begin(e, nm + "matmul-gemm", e->sc, &tg));
-            TRY(gemm(e, 0, 0, e->n, y.out, y.in, H, ldH, y.W, y.out, e->HW, up4(y.out), &bias));
+            TRY(gemm(e, 0, 0, e->n, y.out, y.in, H, ldH, y.Wt, y.ldw, e->HW, up4(y.out), &bias));
             TRY(timer_end(e, e->sc, tg));
             TRY(dist_spmm(e, 0, e->HW, y.Z, y.out, y.activation ? &act : nullptr, nm));
         } else {
@@ -595,7 +613,7 @@ int forward(eng *e) {
             TRY(dist_spmm(e, 0, H, AH, y.in, nullptr, nm));
             act.bias = y.b;
             TRY(timer_begin(e, nm + "matmul-gemm", e->sc, &tg));
-            TRY(gemm(e, 0, 0, e->n, y.out, y.in, AH, up4(y.in), y.W, y.out, y.Z, up4(y.out), &act));
+            TRY(gemm(e, 0, 0, e->n, y.out, y.in, AH, up4(y.in), y.Wt, y.ldw, y.Z, up4(y.out), &act));
             TRY(timer_end(e, e->sc, tg));
         }
         H = y.Z;
@@ -637,7 +655,7 @@ int backward(eng *e) {
             TRY(timer_begin(e, nm + "matmul-gemm", e->sc, &tg));
             TRY(mggcn_colsum_f32(e->sc, e->n, y.out, GHW, ldo, y.Gb, e->ws_colsum, e->ws_colsum_bytes));
             TRY(gemm(e, 1, 0, y.in, y.out, e->n, Hin, ldHin, GHW, ldo, y.GW, y.out, nullptr));
-            if (!first) TRY(gemm(e, 0, 1, e->n, y.in, y.out, GHW, ldo, y.W, y.out, Tprev, ldi, &dact));
+            if (!first) TRY(gemm(e, 0, 1, e->n, y.in, y.out, GHW, ldo, y.Wt, y.ldw, Tprev, ldi, &dact));
             TRY(timer_end(e, e->sc, tg));
         } else {
             // the reference uses the raw layer input H as the GEMM input here
@@ -646,7 +664,7 @@ int backward(eng *e) {
             TRY(timer_begin(e, nm + "matmul-gemm", e->sc, &tg));
             TRY(mggcn_colsum_f32(e->sc, e->n, y.out, T, ldo, y.Gb, e->ws_colsum, e->ws_colsum_bytes));
             TRY(gemm(e, 1, 0, y.in, y.out, e->n, Xin, ldXin, T, ldo, y.GW, y.out, nullptr));
-            if (!first) TRY(gemm(e, 0, 1, e->n, y.in, y.out, T, ldo, y.W, y.out, e->HW, ldi, nullptr));
+            if (!first) TRY(gemm(e, 0, 1, e->n, y.in, y.out, T, ldo, y.Wt, y.ldw, e->HW, ldi, nullptr));
             TRY(timer_end(e, e->sc, tg));
             if (!first) TRY(dist_spmm(e, 1, e->HW, Tprev, y.in, &dact, nm));
         }
@@ -914,6 +932,16 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
             bo += (size_t)y.out;
         }
         E_CUDA(cudaMemcpy(e->params, host.data(), e->n_params * 4, cudaMemcpyDefault));
+        for (int l = 0; l < e->L; ++l) {
+            layer_t &y = e->layers[l];
+            y.Wt = y.W;
+            y.ldw = y.out;
+            if (y.out % 4 != 0 || (reinterpret_cast<uintptr_t>(y.W) & 15) != 0) {
+                y.ldw = up4(y.out);
+                E_CUDA(cudaMalloc(&y.Wpad, (size_t)(y.in * y.ldw) * sizeof(float)));
+                y.Wt = y.Wpad;
+            }
+        }
     }
 
     if (e->P > 1 && !e->p2p) {
@@ -1321,6 +1349,8 @@ void mggcn_engine_destroy(mggcn_engine_t *e) {
     if (e->sc) cudaStreamSynchronize(e->sc);
     if (e->sm && e->sm != e->sc) cudaStreamSynchronize(e->sm);
     if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
+    for (layer_t &y : e->layers)
+        if (y.Wpad) cudaFree(y.Wpad);
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
     for (int r = 0; r < e->P; ++r)
         if (e->peer_opened[r]) cudaIpcCloseMemHandle(e->peer_arena[r]);
