@@ -166,3 +166,23 @@ def test_two_gpu_engine_matches_oracle(cuda, comm, graph):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     assert "dist check ok" in r.stdout
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_four_gpu_grouped_exchange_matches_oracle(cuda, graph):
+    """World 4: the grouped exchange multiplies stages 2-3 in one launch over the all-gather buffer (a group with
+    more than one block only exists from 4 ranks on).  Same checker as the 2-GPU test: per-layer outputs, weight
+    gradients and 10 epochs of loss against the oracle."""
+    import os
+    import subprocess
+    import sys
+    if cuda.cuda.device_count() < 4:
+        pytest.skip("needs 4 GPUs (gpurun --gpus 4)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "4", "--master-addr",
+           "127.0.0.1", "--master-port", "29614", os.path.join(root, "tests", "dist_engine_check.py"), "--comm", "p2p-grouped"]
+    if graph:
+        cmd.append("--graph")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert "dist check ok" in r.stdout
