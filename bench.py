@@ -373,7 +373,9 @@ def main():
         dom = [v for k, v in med.items() if k.endswith("_0_matmul-spmm") and not k.startswith(f"{len(sizes) - 2}_")]
         dom_ms = float(np.mean(dom)) if dom else float("nan")
         alg = spmm_alg_bytes(n_loc, N, dom_nnz, F)
-        dom_name = (f"spmm_kernel<32,1,4> forward, F={F}, whole matrix" if P == 1 else
+        sliced = 64e6 < N * F * 4 <= 124e6 and F % 8 == 0 and F >= 128 and not any(t.startswith("slices=") for t in args.tune)
+        dom_name = ((f"spmm_kernel<16,1,4> x2 (two {F // 2}-wide column windows, automatic feature slicing) forward, F={F}, whole matrix"
+                     if sliced else f"spmm_kernel<32,1,4> forward, F={F}, whole matrix") if P == 1 else
                     f"spmm_kernel<32,1,4> own block + spmm_kernel<32,1,4,gathered> remote blocks, forward, F={F}, block row {n_loc}x{N} "
                     "(the gathered launch waits on-device for the peers' blocks)")
     else:
@@ -430,8 +432,10 @@ def main():
                      "alg_bytes_per_launch": alg, "launch_ms": dom_ms,
                      "gather_GBps": (dom_nnz * F * 4 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 else None,
                      "GFLOPs": (2 * dom_nnz * F / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 else None,
-                     "note": "B (119 MB at F=128) is gathered avg-degree (~490) times: the kernel is L1/L2-gather bound, "
-                             "not HBM bound (SURVEY.md hard part 1); gather_GBps is the operand traffic it sustains"},
+                     "note": "B (119 MB at F=128) is gathered avg-degree (~490) times: the kernel is bound by the L2->SM "
+                             "return path (l1tex 88 %, lts 84 % of peak in ncu), not by HBM (SURVEY.md hard part 1); "
+                             "gather_GBps is the operand traffic it sustains; achieved/frac use the algorithmic bytes "
+                             "of ONE pass over the operands and launch_ms is the whole aggregation"},
         "breakdown_ms": {"spmm": spmm_ms, "gemm": gemm_ms, "exchange": xfer_ms,
                          "loss": sum(v for k, v in med.items() if k.endswith("loss-layer")),
                          "adam": med.get("adam-update"), "allreduce": med.get("allreduce"),

@@ -30,6 +30,7 @@
 using namespace mggcn;
 
 namespace mggcn {
+void spmm_touched_cols_hint(int64_t n);
 int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx,
                   const float *vals, float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
                   float beta, const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws, const spmm_gather &g);
@@ -440,8 +441,15 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
                 MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sc, e->ev_xfer[g], 0));
             }
             TRY(timer_begin(e, tname + std::to_string(g) + "_matmul-spmm-stage", e->sc, &t_s));
-            TRY(mggcn_spmm_csr_f32_i32(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, g == 0 ? B : e->gather, ld, C, ld,
-                                       (int)F, 1.f, g == 0 ? 0.f : 1.f, g == G - 1 ? epi : nullptr, a.plan, e->ws_spmm));
+            int64_t touched = 0;  // a group's CSR addresses the whole all-gather buffer but reads its own blocks only
+            for (int s = e->groups[g].first; s < e->groups[g].second; ++s)
+                touched += (int64_t)e->cuts[(e->rank + s) % P + 1] - (int64_t)e->cuts[(e->rank + s) % P];
+            spmm_touched_cols_hint(touched);
+            const int rc_g = mggcn_spmm_csr_f32_i32(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, g == 0 ? B : e->gather, ld,
+                                                    C, ld, (int)F, 1.f, g == 0 ? 0.f : 1.f, g == G - 1 ? epi : nullptr, a.plan,
+                                                    e->ws_spmm);
+            spmm_touched_cols_hint(-1);
+            TRY(rc_g);
             TRY(timer_end(e, e->sc, t_s));
         }
         TRY(timer_end(e, e->sc, t_all));

@@ -63,6 +63,8 @@ int g_unroll = 4;     // gathers in flight per lane (4 or 8)
 int g_threads = 64;   // CTA size
 int g_policy = 1;     // 1: L2 evict_last for B, evict_first for the CSR stream; 0: plain loads
 int g_split = 0;      // row-split threshold of new plans; 0 = chosen from the matrix (see plan_create)
+int g_slices = 0;     // k > 1: run as k launches over F/k-wide column windows of B and C; 0: k = 2 when B (cols x F floats)
+                      // is larger than half of the L2 but its half is not (see spmm_sliced); 1: never
 
 struct spmm_args {
     const spmm_item *items;  // null: natural order, one item per row from rowptr
@@ -534,6 +536,42 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
     return MGGCN_OK;
 }
 
+thread_local int64_t t_touched_cols = -1;
+
+// Feature slicing: k launches over F/k-wide column windows (every window a multiple of 4 floats, >= 32 wide).
+int spmm_sliced(cudaStream_t st, int64_t rows, int64_t cols, const void *rowptr, int rowptr64, const uint32_t *colidx,
+                const float *vals, const float *B, int64_t ldb, float *C, int64_t ldc, int F, float alpha, float beta,
+                const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws) {
+    // Why: B is the operand with reuse, and the two L2 halves of the chip each keep their own copy of a line, so
+    // B stays resident only up to about half of the 126 MB.  At reddit shape (119 MB at F = 128) the unsliced
+    // kernel re-reads B from DRAM 9 times over (10.7 GB per launch); it is not DRAM-bound, but inside a training
+    // loop the board runs at its power cap and the DRAM traffic costs SM clock: two 64-wide windows measured
+    // 21.3 ms/epoch at 1.78 GHz against 23.2 ms at 1.60 GHz.  The sums per output element are the same either way.
+    // At 2 GPUs (blocks of 60 MB) slicing costs 2.5 % instead, hence the lower bound of 64 MB; callers whose CSR
+    // touches only part of B's rows (the engine's grouped launches) say so through spmm_touched_cols_hint.
+    int k = g_slices;
+    if (k == 0) {
+        const double bytes = (double)(t_touched_cols >= 0 ? t_touched_cols : cols) * (double)F * 4.0;
+        k = (bytes > 64e6 && bytes <= 124e6 && F % 8 == 0 && F / 2 >= 64) ? 2 : 1;
+    }
+    if (k <= 1 || F % (4 * k) != 0 || F / k < 32)
+        return spmm_dispatch(st, rows, cols, rowptr, rowptr64, colidx, vals, B, ldb, C, ldc, F, alpha, beta, epi, plan, ws);
+    const int w = F / k;
+    for (int i = 0; i < k; ++i) {
+        mggcn_epilogue e2{};
+        if (epi) {
+            e2 = *epi;
+            if (e2.bias) e2.bias += i * w;
+            if (e2.aux) e2.aux += i * w;
+            if (e2.keep_mask) e2.keep_mask += i * w;
+        }
+        const int rc = spmm_dispatch(st, rows, cols, rowptr, rowptr64, colidx, vals, B + i * w, ldb, C + i * w, ldc, w, alpha,
+                                     beta, epi ? &e2 : nullptr, plan, ws);
+        if (rc) return rc;
+    }
+    return MGGCN_OK;
+}
+
 template <typename idx_t>
 int plan_create(int64_t rows, const idx_t *rowptr, int split_nnz, mggcn_spmm_plan_t **out) {
     if (!out || rows < 0 || (rows > 0 && !rowptr)) return fail(MGGCN_E_INVALID, "bad argument");
@@ -609,6 +647,8 @@ int plan_create(int64_t rows, const idx_t *rowptr, int split_nnz, mggcn_spmm_pla
 }  // namespace
 
 namespace mggcn {
+// engine.cu: rows of B the next SpMM call of this thread really gathers from (-1: all `cols` of them)
+void spmm_touched_cols_hint(int64_t n) { t_touched_cols = n; }
 // engine.cu: the staged exchange folded into one launch
 int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx,
                   const float *vals, float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
@@ -642,16 +682,16 @@ int mggcn_spmm_csr_f32_i32(mggcn_stream_t stream, int64_t rows, int64_t cols, co
                            const uint32_t *colidx, const float *vals, const float *B, int64_t ldb,
                            float *C, int64_t ldc, int F, float alpha, float beta,
                            const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws) {
-    return spmm_dispatch(static_cast<cudaStream_t>(stream), rows, cols, rowptr, 0, colidx, vals, B, ldb,
-                         C, ldc, F, alpha, beta, epi, plan, ws);
+    return spmm_sliced(static_cast<cudaStream_t>(stream), rows, cols, rowptr, 0, colidx, vals, B, ldb,
+                       C, ldc, F, alpha, beta, epi, plan, ws);
 }
 
 int mggcn_spmm_csr_f32_i64(mggcn_stream_t stream, int64_t rows, int64_t cols, const uint64_t *rowptr,
                            const uint32_t *colidx, const float *vals, const float *B, int64_t ldb,
                            float *C, int64_t ldc, int F, float alpha, float beta,
                            const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws) {
-    return spmm_dispatch(static_cast<cudaStream_t>(stream), rows, cols, rowptr, 1, colidx, vals, B, ldb,
-                         C, ldc, F, alpha, beta, epi, plan, ws);
+    return spmm_sliced(static_cast<cudaStream_t>(stream), rows, cols, rowptr, 1, colidx, vals, B, ldb,
+                       C, ldc, F, alpha, beta, epi, plan, ws);
 }
 
 int mggcn_spmm_plan_create_i32(int64_t rows, const uint32_t *rowptr_host, int split_nnz,
@@ -682,6 +722,7 @@ int mggcn_tune(const char *key, int value) {
     else if (!strcmp(key, "threads")) slot = &g_threads;
     else if (!strcmp(key, "policy")) slot = &g_policy;
     else if (!strcmp(key, "split")) slot = &g_split;
+    else if (!strcmp(key, "slices")) slot = &g_slices;
     else if (!strcmp(key, "gemm_tc")) slot = &mggcn::g_gemm_tc;
     else if (!strcmp(key, "gemm_kgroup")) slot = &mggcn::g_gemm_kgroup;
     if (!slot) return fail(MGGCN_E_INVALID, "unknown tuning key %s", key);
