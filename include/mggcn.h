@@ -214,6 +214,13 @@ MGGCN_API int mggcn_csr_block_fill(int64_t rows, const uint64_t *rowptr, const u
                                    const uint32_t *q, uint64_t *const *blk_rowptr,
                                    uint32_t *const *blk_colidx, float *const *blk_vals);
 
+/* prep.py's compute_comm (test/data/prep.py:232-272): needed[i*Q + j] = number of distinct columns of
+ * block row i (rows p[i]..p[i+1]) that fall into column block j (q[j]..q[j+1]) -- the rows of H_j that
+ * part i gathers from, against the q[j+1]-q[j] rows the staged exchange ships.  Host. */
+MGGCN_API int mggcn_csr_needed_rows(int64_t rows, int64_t cols, const uint64_t *rowptr,
+                                    const uint32_t *colidx, int P, const uint32_t *p, int Q,
+                                    const uint32_t *q, uint64_t *needed);
+
 /* ------------------------------------------------------------------------------------------
  * On-disk formats (test/data/prep.py:46-76; consumer src/matrix.hpp:224-234,486-492).
  *  graph.bin: "PIGO-CSR-v2", u8 sizeof(Label), u8 sizeof(Ordinal), n, m, nrows, ncols,

@@ -89,6 +89,7 @@ _SIGS = {
     "mggcn_csr_transpose": (C.c_int, [_i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "mggcn_csr_block_counts": (C.c_int, [_i64, _vp, _vp, _i32, _vp, _i32, _vp, _vp]),
     "mggcn_csr_block_fill": (C.c_int, [_i64, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
+    "mggcn_csr_needed_rows": (C.c_int, [_i64, _i64, _vp, _vp, _i32, _vp, _i32, _vp, _vp]),
     "mggcn_csr_file_info_read": (C.c_int, [C.c_char_p, C.POINTER(CsrFileInfo)]),
     "mggcn_csr_file_read": (C.c_int, [C.c_char_p, _vp, _vp, _vp]),
     "mggcn_csr_file_write": (C.c_int, [C.c_char_p, _i64, _i64, _vp, _vp, _vp, _i32]),
@@ -214,6 +215,16 @@ class Csr:
                                              cptrs, vptrs))
             out.append([Csr(rps[j], cis[j], vas[j], int(q[j + 1] - q[j])) for j in range(Q)])
         return out if only_row is None else out[0]
+
+    def needed_rows(self, p, q):
+        """prep.py compute_comm (test/data/prep.py:232-272): L[i, j] = distinct columns of block row i inside
+        column block j -- the rows of H_j that part i gathers from."""
+        p = np.ascontiguousarray(p, dtype=np.uint32)
+        q = np.ascontiguousarray(q, dtype=np.uint32)
+        L = np.zeros((len(p) - 1, len(q) - 1), dtype=np.uint64)
+        check(lib().mggcn_csr_needed_rows(self.n, self.m, self.rowptr.ctypes.data, self.colidx.ctypes.data, len(p) - 1,
+                                          p.ctypes.data, len(q) - 1, q.ctypes.data, L.ctypes.data))
+        return L
 
 
 def read_csr(path):

@@ -5,6 +5,7 @@
 // definition.  Everything here is OpenMP-parallel and deterministic for any thread count.
 #include <algorithm>
 #include <omp.h>
+#include <new>
 #include <vector>
 
 #include "common.hpp"
@@ -184,6 +185,43 @@ int mggcn_csr_block_fill(int64_t rows, const uint64_t *rowptr, const uint32_t *c
                 blk_vals[b][pos[j]] = vals[e];
                 pos[j]++;
             }
+        }
+    }
+    return MGGCN_OK;
+}
+
+// test/data/prep.py:232-272 (compute_comm): L[i][j] = number of DISTINCT columns of block row i that fall into
+// column block j, i.e. how many rows of H_j part i really needs -- against the p[j+1]-p[j] rows the staged
+// exchange ships.  One bitmap per block row, set in parallel (idempotent byte stores), counted per column block.
+int mggcn_csr_needed_rows(int64_t rows, int64_t cols, const uint64_t *rowptr, const uint32_t *colidx, int P,
+                          const uint32_t *p, int Q, const uint32_t *q, uint64_t *needed) {
+    if (!rowptr || !p || !q || !needed || P <= 0 || Q <= 0 || rows < 0 || cols < 0) return fail(MGGCN_E_INVALID, "bad argument");
+    if ((int64_t)p[P] > rows || (int64_t)q[Q] > cols) return fail(MGGCN_E_INVALID, "cuts exceed the matrix");
+    if (rowptr[rows] > 0 && !colidx) return fail(MGGCN_E_INVALID, "colidx is null");
+    std::vector<uint8_t> mask;
+    try {
+        mask.resize((size_t)cols);
+    } catch (const std::bad_alloc &) {
+        return fail(MGGCN_E_NOMEM, "out of memory");
+    }
+    for (int i = 0; i < P; ++i) {
+        std::fill(mask.begin(), mask.end(), (uint8_t)0);
+        uint8_t *m = mask.data();
+        const int64_t e0 = (int64_t)rowptr[p[i]], e1 = (int64_t)rowptr[p[i + 1]];
+        bool bad = false;
+#pragma omp parallel for schedule(static) reduction(|| : bad)
+        for (int64_t e = e0; e < e1; ++e) {
+            const uint32_t c = colidx[e];
+            if ((int64_t)c < cols) m[c] = 1;
+            else bad = true;
+        }
+        if (bad) return fail(MGGCN_E_INVALID, "column index outside the matrix");
+        for (int j = 0; j < Q; ++j) {
+            uint64_t cnt = 0;
+            const int64_t c0 = q[j], c1 = q[j + 1];
+#pragma omp parallel for schedule(static) reduction(+ : cnt)
+            for (int64_t c = c0; c < c1; ++c) cnt += m[c];
+            needed[(size_t)i * Q + j] = cnt;
         }
     }
     return MGGCN_OK;

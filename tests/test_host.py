@@ -96,6 +96,37 @@ def test_block_split_bit_exact(mg, orc, P):
     assert total == A.nnz
 
 
+@pytest.mark.parametrize("P", [1, 2, 3, 8])
+def test_needed_rows_match_compute_comm(mg, P):
+    """mggcn_csr_needed_rows against prep.py's compute_comm loop restated in numpy
+    (test/data/prep.py:262-268: mask the columns of block row i, count the mask inside every column block)."""
+    rng = np.random.default_rng(10 + P)
+    n = 517
+    rp, ci, va = random_csr(rng, n, n, 0.03)
+    A = mg.Csr(rp, ci, va, n)
+    cuts = mg.row_cuts(n, P)
+    L = A.needed_rows(cuts, cuts)
+    want = np.zeros((P, P), dtype=np.uint64)
+    for i in range(P):
+        mask = np.zeros(n, dtype=bool)
+        mask[ci[int(rp[cuts[i]]):int(rp[cuts[i + 1]])]] = True
+        for j in range(P):
+            want[i, j] = mask[int(cuts[j]):int(cuts[j + 1])].sum()
+    assert np.array_equal(L, want)
+    # never more than the block holds, and the blocks of a row together hold every distinct column of that row block
+    assert (L <= np.diff(cuts)[None, :]).all()
+    blocks = A.block_rows(cuts, cuts)
+    for i in range(P):
+        for j in range(P):
+            assert int(L[i, j]) == len(np.unique(blocks[i][j].colidx))
+    # an empty matrix needs nothing; a column outside the matrix is refused
+    E = mg.Csr(np.zeros(n + 1, np.uint64), np.zeros(0, np.uint32), np.zeros(0, np.float32), n)
+    assert not E.needed_rows(cuts, cuts).any()
+    bad = mg.Csr(np.array([0, 1], np.uint64), np.array([9], np.uint32), np.ones(1, np.float32), 4)
+    with pytest.raises(mg.MggcnError):
+        bad.needed_rows(np.array([0, 1], np.uint32), np.array([0, 4], np.uint32))
+
+
 def test_generator_emulates_prep(mg):
     """prep.py:101-126: N, F padded to x8, one self-loop per node, unit weights, symmetric pattern;
     padding rows are isolated (self-loop only), zero features, label 0."""
