@@ -373,7 +373,7 @@ def main():
         dom = [v for k, v in med.items() if k.endswith("_0_matmul-spmm") and not k.startswith(f"{len(sizes) - 2}_")]
         dom_ms = float(np.mean(dom)) if dom else float("nan")
         alg = spmm_alg_bytes(n_loc, N, dom_nnz, F)
-        sliced = 64e6 < N * F * 4 <= 124e6 and F % 8 == 0 and F >= 128 and not any(t.startswith("slices=") for t in args.tune)
+        sliced = 90e6 < N * F * 4 <= 124e6 and F % 8 == 0 and F >= 128 and not any(t.startswith("slices=") for t in args.tune)
         dom_name = ((f"spmm_kernel<16,1,4> x2 (two {F // 2}-wide column windows, automatic feature slicing) forward, F={F}, whole matrix"
                      if sliced else f"spmm_kernel<32,1,4> forward, F={F}, whole matrix") if P == 1 else
                     f"spmm_kernel<32,1,4> own block + spmm_kernel<32,1,4,gathered> remote blocks, forward, F={F}, block row {n_loc}x{N} "

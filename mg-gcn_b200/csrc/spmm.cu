@@ -547,12 +547,13 @@ int spmm_sliced(cudaStream_t st, int64_t rows, int64_t cols, const void *rowptr,
     // kernel re-reads B from DRAM 9 times over (10.7 GB per launch); it is not DRAM-bound, but inside a training
     // loop the board runs at its power cap and the DRAM traffic costs SM clock: two 64-wide windows measured
     // 21.3 ms/epoch at 1.78 GHz against 23.2 ms at 1.60 GHz.  The sums per output element are the same either way.
-    // At 2 GPUs (blocks of 60 MB) slicing costs 2.5 % instead, hence the lower bound of 64 MB; callers whose CSR
+    // At 2 GPUs (blocks of 60 MB) slicing costs 2.5 % instead; the crossover between 60 and 119 MB has not been
+    // measured, so the rule only fires from 90 MB (midpoint) up to the L2 size.  Callers whose CSR
     // touches only part of B's rows (the engine's grouped launches) say so through spmm_touched_cols_hint.
     int k = g_slices;
     if (k == 0) {
         const double bytes = (double)(t_touched_cols >= 0 ? t_touched_cols : cols) * (double)F * 4.0;
-        k = (bytes > 64e6 && bytes <= 124e6 && F % 8 == 0 && F / 2 >= 64) ? 2 : 1;
+        k = (bytes > 90e6 && bytes <= 124e6 && F % 8 == 0 && F / 2 >= 64) ? 2 : 1;
     }
     if (k <= 1 || F % (4 * k) != 0 || F / k < 32)
         return spmm_dispatch(st, rows, cols, rowptr, rowptr64, colidx, vals, B, ldb, C, ldc, F, alpha, beta, epi, plan, ws);
