@@ -443,6 +443,22 @@ def main():
         "wall_ms_per_step": ms_wall, "prep_s": prep_s,
         "loss": loss_sum / N if P == 1 else None,
     }
+    if P > 1:
+        # exchange against the NVLink roofline (BASELINE.json north_star): bytes this rank receives per epoch =
+        # sum over the aggregations of (P-1)/P * N * ld * 4, over the time its copies are in flight (eager timers)
+        try:
+            widths = [a for k, a in layer_plan(sizes) if k == "spmm"]
+            rx = sum((P - 1) / P * N * ((w + 3) // 4 * 4) * 4 for w in widths)
+            out["exchange"] = {"rx_bytes_per_rank_per_epoch": int(rx), "copy_ms_per_epoch": xfer_ms,
+                               "GBps": (rx / (xfer_ms * 1e-3) / 1e9) if xfer_ms > 0 else None,
+                               "nvlink_peak_GBps": 900.0,
+                               "nvlink_frac": (rx / (xfer_ms * 1e-3) / 1e9 / 900.0) if xfer_ms > 0 else None,
+                               "epoch_minus_compute_ms": ms_dev - (spmm_ms + gemm_ms + out["breakdown_ms"]["loss"]
+                                                                   + (med.get("adam-update") or 0.0)),
+                               "note": "copies run on the exchange stream behind the SpMM launches of earlier stages; "
+                                       "spmm in breakdown_ms already contains any time a launch waited for a block"}
+        except Exception as ex:  # accounting only: never lose the line
+            out["exchange"] = {"error": repr(ex)}
     if cpu:
         out["cpu_baseline"] = cpu
     emit(out)
