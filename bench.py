@@ -453,8 +453,6 @@ def main():
                                "GBps": (rx / (xfer_ms * 1e-3) / 1e9) if xfer_ms > 0 else None,
                                "nvlink_peak_GBps": 900.0,
                                "nvlink_frac": (rx / (xfer_ms * 1e-3) / 1e9 / 900.0) if xfer_ms > 0 else None,
-                               "epoch_minus_compute_ms": ms_dev - (spmm_ms + gemm_ms + out["breakdown_ms"]["loss"]
-                                                                   + (med.get("adam-update") or 0.0)),
                                "note": "copies run on the exchange stream behind the SpMM launches of earlier stages; "
                                        "spmm in breakdown_ms already contains any time a launch waited for a block"}
         except Exception as ex:  # accounting only: never lose the line
