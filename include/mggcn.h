@@ -126,11 +126,29 @@ MGGCN_API int mggcn_spmm_plan_create_i32(int64_t rows, const uint32_t *rowptr_ho
                                          int split_nnz, mggcn_spmm_plan_t **out);
 MGGCN_API int mggcn_spmm_plan_create_i64(int64_t rows, const uint64_t *rowptr_host,
                                          int split_nnz, mggcn_spmm_plan_t **out);
+/* a2, 2-D schedule.  When B (cols x F floats) is far larger than the L2 every gather of the plain plan is a DRAM
+ * sector read (products-shape, F = 256: 122 GB of DRAM traffic for 6 GB of operands).  A blocked plan cuts the
+ * columns into blocks whose rows of B -- times a feature window chosen at launch -- stay L2-resident; the SpMM
+ * entry points then run (feature windows) x (column blocks) launches over the SAME rowptr / colidx / vals arrays,
+ * accumulating C between blocks.  Needs a host copy of colidx; rows must hold their columns ascending in
+ * key(c) = (c - col_rot) mod cols and inside [0, col_span) (col_rot = 0, col_span = cols: any sorted CSR).
+ * F_hint: the widest F this plan will serve.  The block count comes from a DRAM-traffic model and is 1 (= the plain
+ * plan) whenever blocking would not pay; mggcn_tune("blocks", k) forces it. */
+MGGCN_API int mggcn_spmm_plan_create_blocked_i32(int64_t rows, int64_t cols, const uint32_t *rowptr_host,
+                                                 const uint32_t *colidx_host, uint32_t col_rot,
+                                                 int64_t col_span, int F_hint, int split_nnz,
+                                                 mggcn_spmm_plan_t **out);
+/* number of column blocks of a plan (1 for a plain plan) */
+MGGCN_API int mggcn_spmm_plan_blocks(const mggcn_spmm_plan_t *plan);
 MGGCN_API size_t mggcn_spmm_plan_workspace_bytes(const mggcn_spmm_plan_t *plan, int F);
 MGGCN_API void mggcn_spmm_plan_destroy(mggcn_spmm_plan_t *plan);
-/* Tuning knobs for experiments ("unroll", "threads", "policy", "split"); a negative value only queries.
+/* Tuning knobs for experiments ("unroll", "threads", "policy", "split", "slices", "blocks", "window", "tile_mb",
+ * "gemm_tc", "gemm_kgroup", "skip_exchange"); a negative value only queries.
  * Returns the old value or MGGCN_E_INVALID for an unknown key. */
 MGGCN_API int mggcn_tune(const char *key, int value);
+/* Thread-local text naming the kernel instance and schedule the last SpMM call of this thread launched, e.g.
+ * "spmm_kernel<16,1,4,4,exact> grid=.. cta=64 F=64 x 2 feature window(s) of 64 x 1 column block(s) of 232968". */
+MGGCN_API const char *mggcn_last_spmm_config(void);
 
 /* ------------------------------------------------------------------------------------------
  * a12 / N1. Dense transform, row-major:  C = A(op) * B(op) [+ bias] [activation] [+ beta*C]
@@ -260,6 +278,14 @@ MGGCN_API int mggcn_gen_graph_begin(int64_t n_raw, int64_t target_directed_edges
                                     int64_t *n_padded, int64_t *nnz);
 MGGCN_API int mggcn_gen_graph_finish(mggcn_gen_t *g, uint64_t *rowptr, uint32_t *colidx,
                                      float *vals);
+/* N4. Rows [row_begin, row_end) of the graph the same arguments give mggcn_gen_graph_begin -- entry for entry the
+ * same rows (global column ids), built without the rest of the graph: every rank of a 1-D row partition generates
+ * its own block row (papers100M-shape: 3.2 B entries never exist in one place).  Finish with
+ * mggcn_gen_graph_finish (rowptr has row_end - row_begin + 1 entries and starts at 0). */
+MGGCN_API int mggcn_gen_rows_begin(int64_t n_raw, int64_t target_directed_edges, int degree_model,
+                                   double gamma, int64_t max_deg, uint64_t seed, int permute,
+                                   int64_t row_begin, int64_t row_end, mggcn_gen_t **out,
+                                   int64_t *n_padded, int64_t *nnz_rows);
 /* features ~ U(-1,1) for raw rows/cols, zero in the padding; labels uniform in [0,C), 0 in padding.
  * `seed`/`permute` must match the graph's so rows follow the same vertex permutation.
  * Counter-based, so the result does not depend on the thread count. */
@@ -267,6 +293,12 @@ MGGCN_API int mggcn_gen_features(int64_t n_raw, int64_t n_padded, int64_t f_raw,
                                  uint64_t seed, int permute, float *out);
 MGGCN_API int mggcn_gen_labels(int64_t n_raw, int64_t n_padded, int num_classes, uint64_t seed,
                                int permute, int32_t *out);
+/* rows [row_begin, row_end) of the two above (out holds row_end - row_begin rows) */
+MGGCN_API int mggcn_gen_features_rows(int64_t n_raw, int64_t n_padded, int64_t f_raw,
+                                      int64_t f_padded, uint64_t seed, int permute, int64_t row_begin,
+                                      int64_t row_end, float *out);
+MGGCN_API int mggcn_gen_labels_rows(int64_t n_raw, int64_t n_padded, int num_classes, uint64_t seed,
+                                    int permute, int64_t row_begin, int64_t row_end, int32_t *out);
 /* Weight init of the reference: std::default_random_engine(99) re-seeded per matrix,
  * uniform(-g, g), g = gain * sqrt(3 / rows)   (src/matrix.hpp:539-545). */
 MGGCN_API int mggcn_init_weights(int64_t rows, int64_t cols, float gain, float *out);

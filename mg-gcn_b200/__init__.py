@@ -70,6 +70,9 @@ _SIGS = {
                                               _i32, _i32, _vp, _vp, _vp, C.POINTER(Epilogue), _vp, _vp]),
     "mggcn_spmm_plan_create_i32": (C.c_int, [_i64, _vp, _i32, C.POINTER(_vp)]),
     "mggcn_spmm_plan_create_i64": (C.c_int, [_i64, _vp, _i32, C.POINTER(_vp)]),
+    "mggcn_spmm_plan_create_blocked_i32": (C.c_int, [_i64, _i64, _vp, _vp, C.c_uint32, _i64, _i32, _i32, C.POINTER(_vp)]),
+    "mggcn_spmm_plan_blocks": (C.c_int, [_vp]),
+    "mggcn_last_spmm_config": (C.c_char_p, []),
     "mggcn_spmm_plan_workspace_bytes": (_sz, [_vp, _i32]),
     "mggcn_spmm_plan_destroy": (None, [_vp]),
     "mggcn_tune": (C.c_int, [C.c_char_p, _i32]),
@@ -99,6 +102,10 @@ _SIGS = {
     "mggcn_gen_graph_begin": (C.c_int, [_i64, _i64, _i32, C.c_double, _i64, C.c_uint64, _i32, C.POINTER(_vp),
                                         C.POINTER(_i64), C.POINTER(_i64)]),
     "mggcn_gen_graph_finish": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "mggcn_gen_rows_begin": (C.c_int, [_i64, _i64, _i32, C.c_double, _i64, C.c_uint64, _i32, _i64, _i64, C.POINTER(_vp),
+                                       C.POINTER(_i64), C.POINTER(_i64)]),
+    "mggcn_gen_features_rows": (C.c_int, [_i64, _i64, _i64, _i64, C.c_uint64, _i32, _i64, _i64, _vp]),
+    "mggcn_gen_labels_rows": (C.c_int, [_i64, _i64, _i32, C.c_uint64, _i32, _i64, _i64, _vp]),
     "mggcn_gen_features": (C.c_int, [_i64, _i64, _i64, _i64, C.c_uint64, _i32, _vp]),
     "mggcn_gen_labels": (C.c_int, [_i64, _i64, _i32, C.c_uint64, _i32, _vp]),
     "mggcn_init_weights": (C.c_int, [_i64, _i64, _f32, _vp]),
@@ -278,11 +285,7 @@ SHAPES = {
 def generate(shape, seed=1, permute=True, scale=1.0, features=True):
     """Synthetic stand-in for test/data/prep.py: returns (Csr A, X float32[n, F8], Y int32[n], classes).
     `scale` < 1 shrinks vertices and edges together (same average degree) for tests."""
-    n_raw, edges, f_raw, classes, model, gamma, max_deg = SHAPES[shape] if isinstance(shape, str) else shape
-    if scale != 1.0:
-        n_raw = max(8, int(n_raw * scale))
-        edges = max(n_raw, int(edges * scale))
-        max_deg = max(8, int(max_deg * scale)) if max_deg else 0
+    n_raw, edges, f_raw, classes, model, gamma, max_deg = shape_params(shape, scale)
     g = C.c_void_p()
     n, nnz = C.c_int64(), C.c_int64()
     check(lib().mggcn_gen_graph_begin(n_raw, edges, model, gamma, max_deg, seed, int(permute), C.byref(g),
@@ -300,6 +303,42 @@ def generate(shape, seed=1, permute=True, scale=1.0, features=True):
         Y = np.empty(n.value, dtype=np.int32)
         check(lib().mggcn_gen_labels(n_raw, n.value, classes, seed, int(permute), Y.ctypes.data))
     return A, X, Y, classes
+
+
+def shape_params(shape, scale=1.0):
+    n_raw, edges, f_raw, classes, model, gamma, max_deg = SHAPES[shape] if isinstance(shape, str) else shape
+    if scale != 1.0:
+        n_raw = max(8, int(n_raw * scale))
+        edges = max(n_raw, int(edges * scale))
+        max_deg = max(8, int(max_deg * scale)) if max_deg else 0
+    return n_raw, edges, f_raw, classes, model, gamma, max_deg
+
+
+def padded_n(shape, scale=1.0):
+    return (shape_params(shape, scale)[0] + 7) // 8 * 8
+
+
+def generate_rows(shape, r0, r1, seed=1, permute=True, scale=1.0, features=True):
+    """Rows [r0, r1) of generate(shape, ...): (Csr slab with r1-r0 rows and GLOBAL column ids, X rows, Y rows,
+    classes) -- what one rank of the 1-D row partition needs, built without the rest of the graph."""
+    n_raw, edges, f_raw, classes, model, gamma, max_deg = shape_params(shape, scale)
+    g = C.c_void_p()
+    n, nnz = C.c_int64(), C.c_int64()
+    check(lib().mggcn_gen_rows_begin(n_raw, edges, model, gamma, max_deg, seed, int(permute), r0, r1, C.byref(g),
+                                     C.byref(n), C.byref(nnz)))
+    rowptr = np.empty(r1 - r0 + 1, dtype=np.uint64)
+    colidx = np.empty(nnz.value, dtype=np.uint32)
+    vals = np.empty(nnz.value, dtype=np.float32)
+    check(lib().mggcn_gen_graph_finish(g, rowptr.ctypes.data, colidx.ctypes.data, vals.ctypes.data))
+    slab = Csr(rowptr, colidx, vals, n.value)
+    X = Y = None
+    if features:
+        f8 = (f_raw + 7) // 8 * 8
+        X = np.empty((r1 - r0, f8), dtype=np.float32)
+        check(lib().mggcn_gen_features_rows(n_raw, n.value, f_raw, f8, seed, int(permute), r0, r1, X.ctypes.data))
+        Y = np.empty(r1 - r0, dtype=np.int32)
+        check(lib().mggcn_gen_labels_rows(n_raw, n.value, classes, seed, int(permute), r0, r1, Y.ctypes.data))
+    return slab, X, Y, classes
 
 
 def write_dataset(dirname, A, X, Y, ordinal_bytes=4):
@@ -332,16 +371,27 @@ def make_epilogue(kind=EPI_NONE, slope=0.01, bias=None, aux=None, keep_mask=None
 
 
 class SpmmPlan:
-    def __init__(self, rowptr_host, split_nnz=0):
+    def __init__(self, rowptr_host, split_nnz=0, colidx_host=None, cols=None, F_hint=0, col_rot=0, col_span=0):
+        """Plain plan from the row pointers; with colidx_host (+ cols, F_hint) a column-blocked plan
+        (mggcn_spmm_plan_create_blocked_i32) whose block count the library chooses."""
         rp = np.ascontiguousarray(rowptr_host)
         self.rows = len(rp) - 1
         self.handle = C.c_void_p()
-        if rp.dtype == np.uint64:
+        if colidx_host is not None:
+            rp = rp.astype(np.uint32)
+            ci = np.ascontiguousarray(colidx_host, dtype=np.uint32)
+            check(lib().mggcn_spmm_plan_create_blocked_i32(self.rows, cols, rp.ctypes.data, ci.ctypes.data, col_rot, col_span,
+                                                           F_hint, split_nnz, C.byref(self.handle)))
+        elif rp.dtype == np.uint64:
             check(lib().mggcn_spmm_plan_create_i64(self.rows, rp.ctypes.data, split_nnz, C.byref(self.handle)))
         else:
             rp = rp.astype(np.uint32)
             check(lib().mggcn_spmm_plan_create_i32(self.rows, rp.ctypes.data, split_nnz, C.byref(self.handle)))
         self._ws = None
+
+    @property
+    def blocks(self):
+        return lib().mggcn_spmm_plan_blocks(self.handle)
 
     def workspace(self, F):
         import torch
@@ -571,3 +621,35 @@ def build_rank_engine(A, sizes, world=1, rank=0, device=0, **kw):
     eng.set_adjacency(0, A_T.block_rows(cuts, cuts, only_row=rank))
     eng.set_adjacency(1, A.block_rows(cuts, cuts, only_row=rank))
     return eng, A_T
+
+
+def slab_operands(slab, deg_all, r0):
+    """The two aggregation operands of one rank from its row slab of the UNnormalised graph (unit weights,
+    symmetric pattern, global column ids) and every vertex's degree -- without the global normalise / transpose:
+      forward  operand = rows of A_T:  A_T[i][j] = A[j][i] = 1 / colsum(i) = 1 / deg(i)     (src/main.cpp:143-151)
+      backward operand = rows of A:    A[i][j]   = 1 / colsum(j) = 1 / deg(j)
+    The pattern is symmetric, so both have the slab's pattern; the values are the same IEEE quotients
+    csr_matrix::normalize(true) computes (1.0f / float column sum; the sum of deg ones is exact), so the blocks are
+    bit-identical to normalise -> transpose -> split of the whole graph (tests/test_host.py)."""
+    deg_all = np.ascontiguousarray(deg_all, dtype=np.uint32)
+    n = slab.n
+    inv = (np.float32(1.0) / deg_all.astype(np.float32)).astype(np.float32)
+    row_len = np.diff(slab.rowptr.astype(np.int64))
+    fwd_vals = np.repeat(inv[r0:r0 + n], row_len)
+    bwd_vals = inv[slab.colidx]
+    return Csr(slab.rowptr, slab.colidx, fwd_vals, slab.m), Csr(slab.rowptr, slab.colidx, bwd_vals, slab.m)
+
+
+def build_rank_engine_sharded(slab, deg_all, sizes, world=1, rank=0, device=0, cuts=None, **kw):
+    """build_rank_engine for a rank that holds only its own row slab (generate_rows) plus the degree of every
+    vertex (all-gathered by the caller): no rank ever builds, normalises or transposes the whole graph."""
+    N = slab.m
+    cuts = row_cuts(N, world) if cuts is None else np.ascontiguousarray(cuts, dtype=np.uint32)
+    r0 = int(cuts[rank])
+    assert slab.n == int(cuts[rank + 1]) - r0
+    fwd, bwd = slab_operands(slab, deg_all, r0)
+    eng = Engine(sizes, N, world=world, rank=rank, device=device, cuts=cuts, **kw)
+    local = np.array([0, slab.n], dtype=np.uint32)
+    eng.set_adjacency(0, fwd.block_rows(local, cuts, only_row=0))
+    eng.set_adjacency(1, bwd.block_rows(local, cuts, only_row=0))
+    return eng, fwd, bwd

@@ -30,6 +30,10 @@
 using namespace mggcn;
 
 namespace mggcn {
+// mggcn_tune("skip_exchange", 1): the peer copies of the p2p back-ends are not enqueued (barriers, events and
+// launches stay).  The result is wrong by construction -- it exists to MEASURE how much of an epoch the exchange
+// leaves exposed: exposed = epoch(with copies) - epoch(without).  Never set outside a measurement.
+int g_skip_exchange = 0;
 void spmm_touched_cols_hint(int64_t n);
 int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx,
                   const float *vals, float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
@@ -224,7 +228,10 @@ __global__ void adam_prep_kernel(float *state, float beta1, float beta2) {
     state[2] = (float)(1.0 - pow((double)beta2, (double)t));
 }
 __global__ void adam_dev_kernel(size_t n, float *p, float *g, float *m, float *v, const float *state, float lr,
-                                float beta1, float beta2, float wd, float eps, size_t n_decay) {
+                                float beta1, float beta2, float wd, float eps, size_t n_decay, const int *err) {
+    // a peer that never arrived (barrier / stage-flag timeout) leaves partial sums behind: keep the parameters
+    // as they are, the host sees the error at its next loss() / sync()
+    if (err && err[0] != 0) return;
     const float bc1 = state[1], bc2 = state[2];
     const float step_size = lr / bc1;
     const float a1 = 1.f - beta1, a2 = 1.f - beta2;
@@ -301,7 +308,7 @@ struct mggcn_engine {
     float *gather = nullptr;
     uint32_t *stage_flags = nullptr;
     cudaEvent_t ev_bar = nullptr, ev_copied = nullptr;
-    int64_t maxw = 0, max_block_rows = 0;
+    int64_t maxw = 0, gw = 0, max_block_rows = 0;
     float *params = nullptr, *grads = nullptr, *gsum = nullptr, *adam_m = nullptr, *adam_v = nullptr;
     size_t n_params = 0, n_weights = 0;
     float *adam_state = nullptr;  // t, bc1, bc2
@@ -331,6 +338,7 @@ struct mggcn_engine {
     // graph
     cudaGraphExec_t graph_exec = nullptr;
     float g_lr = 0, g_b1 = 0, g_b2 = 0, g_wd = 0, g_eps = 0;
+    int g_skip = 0;
     int64_t launches_per_epoch = 0;
     bool forward_done = false;
 
@@ -381,11 +389,16 @@ int xbarrier(eng *e, cudaStream_t st) {
     if (slot >= kBarrierSlots) return fail(MGGCN_E_STATE, "too many barriers in one epoch");
     peer_table pt{};
     for (int r = 0; r < e->P; ++r) pt.flags[r] = reinterpret_cast<uint32_t *>(e->peer_arena[r]);
-    // about 10 s of SM clock by default; MGGCN_BARRIER_TIMEOUT_MS shortens it for tests
+    // about 10 s by default; MGGCN_BARRIER_TIMEOUT_MS shortens it for tests.  clock64() ticks at the SM clock.
     static const long long cycles = [] {
         const char *v = getenv("MGGCN_BARRIER_TIMEOUT_MS");
         const long long ms = v && atoll(v) > 0 ? atoll(v) : 10000;
-        return ms * 2000000ll;
+        int dev = 0, khz = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev) != cudaSuccess || khz <= 0) {
+            cudaGetLastError();
+            khz = 2000000;
+        }
+        return ms * (long long)khz;
     }();
     xbarrier_kernel<<<1, 32, 0, st>>>(pt, e->tickets, slot, e->rank, e->P, e->dev_err, cycles);
     MGGCN_LAUNCH_CHECK();
@@ -426,7 +439,9 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
                 const size_t count = ((size_t)e->cuts[blk + 1] - (size_t)e->cuts[blk]) * (size_t)ld;
                 float *dst = e->gather + (size_t)e->cuts[blk] * (size_t)ld;
                 TRY(timer_begin(e, tname + std::to_string(s) + "_matmul-bcast", e->sm, &t_x));
-                if (e->peer_inproc[blk] && !e->capturing) {
+                if (g_skip_exchange) {
+                    // measurement only: see g_skip_exchange
+                } else if (e->peer_inproc[blk] && !e->capturing) {
                     pull_copy_kernel<<<64, 512, 0, e->sm>>>(reinterpret_cast<const float4 *>(e->peer_arena[blk] + off),
                                                             reinterpret_cast<float4 *>(dst), count / 4);
                     MGGCN_LAUNCH_CHECK();
@@ -543,7 +558,9 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
             const size_t count = (size_t)a.cols * (size_t)ld;
             TRY(timer_begin(e, tname + std::to_string(s) + "_matmul-bcast", e->sm, &t_x));
             if (e->p2p) {
-                if (e->peer_inproc[blk] && !e->capturing) {
+                if (g_skip_exchange) {
+                    // measurement only: see g_skip_exchange
+                } else if (e->peer_inproc[blk] && !e->capturing) {
                     // count is a multiple of 4 floats (ld is), both ends are 256-byte aligned arena carvings
                     pull_copy_kernel<<<64, 512, 0, e->sm>>>(reinterpret_cast<const float4 *>(e->peer_arena[blk] + off),
                                                             reinterpret_cast<float4 *>(e->stage[s & 1]), count / 4);
@@ -711,7 +728,7 @@ int adam(eng *e, float lr, float b1, float b2, float wd, float eps) {
     MGGCN_LAUNCH_CHECK();
     const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((e->n_params + 255) / 256, 148 * 4));
     adam_dev_kernel<<<grid, 256, 0, e->sc>>>(e->n_params, e->params, e->gsum, e->adam_m, e->adam_v, e->adam_state, lr,
-                                             b1, b2, wd, eps, e->n_weights);
+                                             b1, b2, wd, eps, e->n_weights, e->dev_err);
     MGGCN_LAUNCH_CHECK();
     TRY(timer_end(e, e->sc, tg));
     return MGGCN_OK;
@@ -783,8 +800,8 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     // the all-gather buffer holds every rank's rows at the widest layer: past 32 GB per rank (papers100M-shape:
     // 57 GB) the grouped form falls back to the double-buffered staged exchange
     if (e->grouped) {
-        int64_t w = 0;
-        for (int i = 0; i <= cfg->num_layers; ++i) w = std::max<int64_t>(w, cfg->sizes[i]);
+        int64_t w = 0;  // widest aggregated operand: a layer aggregates its narrower side (src/gcn.hpp:439,558)
+        for (int l = 0; l < cfg->num_layers; ++l) w = std::max<int64_t>(w, up4(std::min(cfg->sizes[l], cfg->sizes[l + 1])));
         if ((double)cfg->n_global * (double)w * 4.0 > 32.0 * (1ull << 30)) e->grouped = false;
     }
     if (e->grouped) {
@@ -836,7 +853,11 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     e->layers.resize(e->L);
     e->n_weights = 0;
     size_t n_bias = 0;
-    e->maxw = up4(e->sizes[0]);
+    // widths: `maxw` = widest aggregated operand (gemm-first layers aggregate their output, the others their
+    // input) -- it sizes HW, the staging / all-gather buffers and the SpMM workspace; `gw` = widest gradient
+    // handed to the layer below (the input width of layers 1..L-1)
+    e->maxw = 4;
+    e->gw = 4;
     for (int l = 0; l < e->L; ++l) {
         layer_t &y = e->layers[l];
         y.in = e->sizes[l];
@@ -845,30 +866,34 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
         y.gemm_first = y.out <= y.in;     // src/gcn.hpp:439,558
         e->n_weights += (size_t)(y.in * y.out);
         n_bias += (size_t)y.out;
-        e->maxw = std::max(e->maxw, up4(y.out));
+        e->maxw = std::max(e->maxw, up4(y.gemm_first ? y.out : y.in));
+        if (l > 0) e->gw = std::max(e->gw, up4(y.in));
     }
     e->n_params = e->n_weights + n_bias;
     for (int i = 0; i < e->P; ++i)
         e->max_block_rows = std::max<int64_t>(e->max_block_rows, (int64_t)e->cuts[i + 1] - (int64_t)e->cuts[i]);
     e->ldX = up4(e->sizes[0]);
 
+    // Every per-row buffer is carved for the LARGEST row block of the partition, not for this rank's own: peers
+    // address each other's buffers as (peer arena base + this rank's offset), so the layout must not depend on
+    // the rank even when N % P != 0 makes the blocks uneven.
     for (int l = 0; l < e->L; ++l) {
         const layer_t &y = e->layers[l];
-        e->ws_gemm_bytes = std::max(e->ws_gemm_bytes, mggcn_gemm_workspace_bytes(1, 0, y.in, y.out, e->n));
-        e->ws_colsum_bytes = std::max(e->ws_colsum_bytes, mggcn_colsum_workspace_bytes(e->n, y.out));
+        e->ws_gemm_bytes = std::max(e->ws_gemm_bytes, mggcn_gemm_workspace_bytes(1, 0, y.in, y.out, e->max_block_rows));
+        e->ws_colsum_bytes = std::max(e->ws_colsum_bytes, mggcn_colsum_workspace_bytes(e->max_block_rows, y.out));
     }
-    e->ws_loss_bytes = mggcn_softmax_xent_workspace_bytes(e->n);
+    e->ws_loss_bytes = mggcn_softmax_xent_workspace_bytes(e->max_block_rows);
 
     // ---- arena
-    const size_t n = (size_t)e->n;
+    const size_t n = (size_t)e->max_block_rows;
     size_t total = 0;
     auto need = [&](size_t bytes) { total += up256(bytes); };
     need(sizeof(uint32_t) * kBarrierSlots * kMaxRanks);           // flags
     need(n * (size_t)e->ldX * 4);                                  // X
     need(n * 4);                                                   // Y
     need(n * (size_t)e->maxw * 4);                                 // HW
-    need(n * (size_t)e->maxw * 4);                                 // G0
-    need(n * (size_t)e->maxw * 4);                                 // G1
+    need(n * (size_t)e->gw * 4);                                   // G0
+    need(n * (size_t)e->gw * 4);                                   // G1
     if (e->fused || e->grouped) {
         need((size_t)e->N * (size_t)e->maxw * 4);
         need(64);
@@ -896,8 +921,8 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     e->X = carve<float>(cur, n * (size_t)e->ldX);
     e->Y = carve<int32_t>(cur, n);
     e->HW = carve<float>(cur, n * (size_t)e->maxw);
-    e->G[0] = carve<float>(cur, n * (size_t)e->maxw);
-    e->G[1] = carve<float>(cur, n * (size_t)e->maxw);
+    e->G[0] = carve<float>(cur, n * (size_t)e->gw);
+    e->G[1] = carve<float>(cur, n * (size_t)e->gw);
     if (e->fused || e->grouped) {
         e->gather = carve<float>(cur, (size_t)e->N * (size_t)e->maxw);
         e->stage_flags = carve<uint32_t>(cur, 16);
@@ -969,10 +994,31 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     return MGGCN_OK;
 }
 
+// 0 = well formed; 1 = rowptr[0] != 0; 2 = rowptr not monotone; 3 = a column id >= cols
+static int validate_csr(int64_t rows, int64_t cols, const uint64_t *rp, const uint32_t *ci) {
+    if (rp[0] != 0) return 1;
+    int bad = 0;
+#pragma omp parallel for schedule(static) reduction(max : bad)
+    for (int64_t r = 0; r < rows; ++r) {
+        if (rp[r + 1] < rp[r]) { bad = std::max(bad, 2); continue; }
+        for (uint64_t k = rp[r]; k < rp[r + 1]; ++k)
+            if ((int64_t)ci[k] >= cols) { bad = std::max(bad, 3); break; }
+    }
+    return bad;
+}
+
 int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *const *blk_rowptr,
                                const uint32_t *const *blk_colidx, const float *const *blk_vals) {
     if (!e || which < 0 || which > 1 || !blk_rowptr || !blk_colidx || !blk_vals) return fail(MGGCN_E_INVALID, "bad argument");
     TRY(set_dev(e));
+    // the kernels gather B + colidx * ld unchecked: refuse malformed blocks here, once, on the host
+    for (int j = 0; j < e->P; ++j) {
+        if (!blk_rowptr[j] || ((!blk_colidx[j] || !blk_vals[j]) && blk_rowptr[j][e->n] > 0))
+            return fail(MGGCN_E_INVALID, "block %d has a null array", j);
+        const int rc = validate_csr(e->n, (int64_t)e->cuts[j + 1] - (int64_t)e->cuts[j], blk_rowptr[j], blk_colidx[j]);
+        if (rc) return fail(MGGCN_E_FORMAT, "adjacency block (%d, %d) is malformed: %s", e->rank, j,
+                            rc == 1 ? "row pointers do not start at 0" : rc == 2 ? "row pointers decrease" : "column index out of range");
+    }
     size_t ws = e->ws_spmm_bytes;
     // merged CSRs over ranges of stages (global column ids into the all-gather buffer, every row in stage order:
     // blocks rank+s0, rank+s0+1, ... cyclically).  Gathered form: slot 0 = all remote stages [1, P) in one CSR, so
@@ -1028,7 +1074,16 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
         MGGCN_CUDA_TRY(cudaMalloc(&a.vals, va.size() * 4));
         MGGCN_CUDA_TRY(cudaMemcpy(a.colidx, ci.data(), (size_t)nnz * 4, cudaMemcpyDefault));
         MGGCN_CUDA_TRY(cudaMemcpy(a.vals, va.data(), (size_t)nnz * 4, cudaMemcpyDefault));
-        TRY(mggcn_spmm_plan_create_i32(a.rows, rp32.data(), 0, &a.plan));
+        if (e->grouped) {
+            // the group's columns are the blocks rank+s0 .. rank+s1-1 (cyclic) of the all-gather buffer; far beyond
+            // the L2 (products-shape) the plan cuts them into column blocks (2-D schedule, csrc/spmm.cu)
+            int64_t span = 0;
+            for (int st = s0; st < s1; ++st) span += (int64_t)e->cuts[(e->rank + st) % P + 1] - (int64_t)e->cuts[(e->rank + st) % P];
+            TRY(mggcn_spmm_plan_create_blocked_i32(a.rows, a.cols, rp32.data(), ci.data(), e->cuts[(e->rank + s0) % P], span,
+                                                   (int)e->maxw, 0, &a.plan));
+        } else {
+            TRY(mggcn_spmm_plan_create_i32(a.rows, rp32.data(), 0, &a.plan));
+        }
         ws = std::max(ws, mggcn_spmm_plan_workspace_bytes(a.plan, (int)e->maxw));
     }
     for (int j = 0; j < e->P; ++j) {
@@ -1052,7 +1107,8 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
         MGGCN_CUDA_TRY(cudaMalloc(&a.vals, std::max<size_t>((size_t)a.nnz, 1) * 4));
         MGGCN_CUDA_TRY(cudaMemcpy(a.colidx, blk_colidx[j], (size_t)a.nnz * 4, cudaMemcpyDefault));
         MGGCN_CUDA_TRY(cudaMemcpy(a.vals, blk_vals[j], (size_t)a.nnz * 4, cudaMemcpyDefault));
-        TRY(mggcn_spmm_plan_create_i32(a.rows, rp32.data(), 0, &a.plan));
+        if (e->fused) TRY(mggcn_spmm_plan_create_i32(a.rows, rp32.data(), 0, &a.plan));
+        else TRY(mggcn_spmm_plan_create_blocked_i32(a.rows, a.cols, rp32.data(), blk_colidx[j], 0, a.cols, (int)e->maxw, 0, &a.plan));
         ws = std::max(ws, mggcn_spmm_plan_workspace_bytes(a.plan, (int)e->maxw));
     }
     if (ws > e->ws_spmm_bytes) {
@@ -1186,7 +1242,8 @@ int mggcn_engine_adam_update(mggcn_engine_t *e, float lr, float beta1, float bet
 // drives several engines must prepare all of them BEFORE it launches any (a launched engine spins in
 // its first barrier until its peers are launched too).
 static int ensure_graph(mggcn_engine_t *e, float lr, float beta1, float beta2, float wd, float eps) {
-    if (e->graph_exec && (lr != e->g_lr || beta1 != e->g_b1 || beta2 != e->g_b2 || wd != e->g_wd || eps != e->g_eps)) {
+    if (e->graph_exec && (lr != e->g_lr || beta1 != e->g_b1 || beta2 != e->g_b2 || wd != e->g_wd || eps != e->g_eps ||
+                          e->g_skip != g_skip_exchange)) {
         cudaGraphExecDestroy(e->graph_exec);
         e->graph_exec = nullptr;
     }
@@ -1225,6 +1282,7 @@ static int ensure_graph(mggcn_engine_t *e, float lr, float beta1, float beta2, f
     MGGCN_CUDA_TRY(cudaGraphUpload(e->graph_exec, e->sc));
     MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
     e->g_lr = lr; e->g_b1 = beta1; e->g_b2 = beta2; e->g_wd = wd; e->g_eps = eps;
+    e->g_skip = g_skip_exchange;
     return MGGCN_OK;
 }
 
@@ -1253,13 +1311,7 @@ int mggcn_engine_epoch(mggcn_engine_t *e, float lr, float beta1, float beta2, fl
     return MGGCN_OK;
 }
 
-int mggcn_engine_sync(mggcn_engine_t *e) {
-    if (!e) return fail(MGGCN_E_INVALID, "null engine");
-    TRY(set_dev(e));
-    MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
-    if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sm));
-    int err[4] = {0, 0, 0, 0};
-    MGGCN_CUDA_TRY(cudaMemcpy(err, e->dev_err, sizeof err, cudaMemcpyDefault));
+static int report_dev_err(const mggcn_engine_t *e, const int *err) {
     if (err[0] == 2) return fail(MGGCN_E_STATE, "a feature block of a peer never arrived (stage flag timed out)");
     if (err[0])
         return fail(MGGCN_E_STATE, "peer barrier timed out (a rank is missing or died): rank %d, barrier %d waited for "
@@ -1267,12 +1319,25 @@ int mggcn_engine_sync(mggcn_engine_t *e) {
     return MGGCN_OK;
 }
 
+int mggcn_engine_sync(mggcn_engine_t *e) {
+    if (!e) return fail(MGGCN_E_INVALID, "null engine");
+    TRY(set_dev(e));
+    MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
+    if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sm));
+    int err[4] = {0, 0, 0, 0};
+    MGGCN_CUDA_TRY(cudaMemcpy(err, e->dev_err, sizeof err, cudaMemcpyDefault));
+    return report_dev_err(e, err);
+}
+
 int mggcn_engine_loss(mggcn_engine_t *e, double *loss_sum, double *correct) {
     if (!e) return fail(MGGCN_E_INVALID, "null engine");
     TRY(set_dev(e));
     double h[2] = {0, 0};
+    int err[4] = {0, 0, 0, 0};
     MGGCN_CUDA_TRY(cudaMemcpyAsync(h, e->loss_out, sizeof h, cudaMemcpyDefault, e->sc));
+    MGGCN_CUDA_TRY(cudaMemcpyAsync(err, e->dev_err, sizeof err, cudaMemcpyDefault, e->sc));
     MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
+    TRY(report_dev_err(e, err));  // a loop that only ever reads the loss must not train on stale peer data silently
     if (loss_sum) *loss_sum = h[0];
     if (correct) *correct = h[1];
     return MGGCN_OK;

@@ -75,15 +75,20 @@ struct alias_table {
 
 }  // namespace
 
-extern "C" {
-
-int mggcn_gen_graph_begin(int64_t n_raw, int64_t target_directed_edges, int degree_model,
-                          double gamma, int64_t max_deg, uint64_t seed, int permute,
-                          mggcn_gen_t **out, int64_t *n_padded, int64_t *nnz) {
+// Rows [r0, r1) of the generated graph (r1 < 0: all of them).  The edge samples are counter-based, so a rank that
+// wants only its row block walks the same sample stream and keeps the pairs that touch its rows: the rows it builds
+// are entry for entry the rows of the whole graph.
+static int gen_rows(int64_t n_raw, int64_t target_directed_edges, int degree_model, double gamma, int64_t max_deg,
+                    uint64_t seed, int permute, int64_t r0, int64_t r1, mggcn_gen_t **out, int64_t *n_padded, int64_t *nnz) {
     if (n_raw <= 0 || target_directed_edges < 0 || !out || !n_padded || !nnz)
         return fail(MGGCN_E_INVALID, "bad argument");
     const int64_t n = (n_raw + 7) / 8 * 8;
     if (n > 0xFFFFFFFFll) return fail(MGGCN_E_UNSUPPORTED, "more than 2^32 vertices");
+    if (r1 < 0) { r0 = 0; r1 = n; }
+    if (r0 < 0 || r0 > r1 || r1 > n) return fail(MGGCN_E_INVALID, "row range [%lld, %lld) outside [0, %lld)", (long long)r0, (long long)r1, (long long)n);
+    const int64_t nl = r1 - r0;
+    const uint32_t lo32 = (uint32_t)r0;
+    auto mine = [&](uint32_t x) { return (uint64_t)x - lo32 < (uint64_t)nl; };
     const int64_t E = target_directed_edges / 2;  // undirected samples; each yields two entries
 
     alias_table tab;
@@ -120,7 +125,8 @@ int mggcn_gen_graph_begin(int64_t n_raw, int64_t target_directed_edges, int degr
     } else if (degree_model != 0) {
         return fail(MGGCN_E_INVALID, "unknown degree model %d", degree_model);
     }
-    const std::vector<uint32_t> perm = make_perm(n, permute ? (seed ? seed : 1) : 0);
+    const bool permuted = permute != 0;
+    const std::vector<uint32_t> perm = permuted ? make_perm(n, seed ? seed : 1) : std::vector<uint32_t>();
 
     auto endpoints = [&](int64_t k, uint32_t &u, uint32_t &v) {
         uint64_t hu = hash2(seed, 2 * (uint64_t)k), hv = hash2(seed, 2 * (uint64_t)k + 1);
@@ -131,39 +137,41 @@ int mggcn_gen_graph_begin(int64_t n_raw, int64_t target_directed_edges, int degr
             u = (uint32_t)(((hu >> 32) * (uint64_t)n_raw) >> 32);
             v = (uint32_t)(((hv >> 32) * (uint64_t)n_raw) >> 32);
         }
-        u = perm[u];
-        v = perm[v];
+        if (permuted) {
+            u = perm[u];
+            v = perm[v];
+        }
     };
 
     // pass 1: degrees (both directions); self pairs are dropped, the self-loop is added later
-    std::vector<std::atomic<uint32_t>> deg((size_t)n);
+    std::vector<std::atomic<uint32_t>> deg((size_t)nl);
     for (auto &d : deg) d.store(0, std::memory_order_relaxed);
 #pragma omp parallel for schedule(static)
     for (int64_t k = 0; k < E; ++k) {
         uint32_t u, v;
         endpoints(k, u, v);
         if (u == v) continue;
-        deg[u].fetch_add(1, std::memory_order_relaxed);
-        deg[v].fetch_add(1, std::memory_order_relaxed);
+        if (mine(u)) deg[u - lo32].fetch_add(1, std::memory_order_relaxed);
+        if (mine(v)) deg[v - lo32].fetch_add(1, std::memory_order_relaxed);
     }
-    std::vector<uint64_t> start((size_t)n + 1, 0);
-    for (int64_t i = 0; i < n; ++i) start[i + 1] = start[i] + deg[i].load(std::memory_order_relaxed);
-    std::vector<uint32_t> raw(start[n]);
-    std::vector<std::atomic<uint64_t>> cursor((size_t)n);
-    for (int64_t i = 0; i < n; ++i) cursor[i].store(start[i], std::memory_order_relaxed);
+    std::vector<uint64_t> start((size_t)nl + 1, 0);
+    for (int64_t i = 0; i < nl; ++i) start[i + 1] = start[i] + deg[i].load(std::memory_order_relaxed);
+    std::vector<uint32_t> raw(start[nl]);
+    std::vector<std::atomic<uint64_t>> cursor((size_t)nl);
+    for (int64_t i = 0; i < nl; ++i) cursor[i].store(start[i], std::memory_order_relaxed);
     // pass 2: scatter (order inside a row is arbitrary here, fixed by the sort below)
 #pragma omp parallel for schedule(static)
     for (int64_t k = 0; k < E; ++k) {
         uint32_t u, v;
         endpoints(k, u, v);
         if (u == v) continue;
-        raw[cursor[u].fetch_add(1, std::memory_order_relaxed)] = v;
-        raw[cursor[v].fetch_add(1, std::memory_order_relaxed)] = u;
+        if (mine(u)) raw[cursor[u - lo32].fetch_add(1, std::memory_order_relaxed)] = v;
+        if (mine(v)) raw[cursor[v - lo32].fetch_add(1, std::memory_order_relaxed)] = u;
     }
     // pass 3: sort + dedup each row, insert the self-loop
-    std::vector<uint32_t> final_deg((size_t)n);
+    std::vector<uint32_t> final_deg((size_t)nl);
 #pragma omp parallel for schedule(dynamic, 256)
-    for (int64_t i = 0; i < n; ++i) {
+    for (int64_t i = 0; i < nl; ++i) {
         uint32_t *b = raw.data() + start[i], *e = raw.data() + start[i + 1];
         std::sort(b, e);
         uint32_t *u = std::unique(b, e);
@@ -171,24 +179,41 @@ int mggcn_gen_graph_begin(int64_t n_raw, int64_t target_directed_edges, int degr
     }
     auto *g = new (std::nothrow) mggcn_gen;
     if (!g) return fail(MGGCN_E_NOMEM, "out of memory");
-    g->n = n;
-    g->rowptr.assign((size_t)n + 1, 0);
-    for (int64_t i = 0; i < n; ++i) g->rowptr[i + 1] = g->rowptr[i] + final_deg[i];
-    g->colidx.resize(g->rowptr[n]);
+    g->n = nl;
+    g->rowptr.assign((size_t)nl + 1, 0);
+    for (int64_t i = 0; i < nl; ++i) g->rowptr[i + 1] = g->rowptr[i] + final_deg[i];
+    g->colidx.resize(g->rowptr[nl]);
 #pragma omp parallel for schedule(dynamic, 256)
-    for (int64_t i = 0; i < n; ++i) {
+    for (int64_t i = 0; i < nl; ++i) {
         const uint32_t *b = raw.data() + start[i];
         const uint32_t cnt = final_deg[i] - 1;
+        const uint32_t self = (uint32_t)(i + r0);
         uint32_t *o = g->colidx.data() + g->rowptr[i];
         uint32_t k = 0;
-        while (k < cnt && b[k] < (uint32_t)i) { *o++ = b[k]; ++k; }
-        *o++ = (uint32_t)i;
+        while (k < cnt && b[k] < self) { *o++ = b[k]; ++k; }
+        *o++ = self;
         while (k < cnt) { *o++ = b[k]; ++k; }
     }
     *out = g;
     *n_padded = n;
-    *nnz = (int64_t)g->rowptr[n];
+    *nnz = (int64_t)g->rowptr[nl];
     return MGGCN_OK;
+}
+
+extern "C" {
+
+int mggcn_gen_graph_begin(int64_t n_raw, int64_t target_directed_edges, int degree_model,
+                          double gamma, int64_t max_deg, uint64_t seed, int permute,
+                          mggcn_gen_t **out, int64_t *n_padded, int64_t *nnz) {
+    return gen_rows(n_raw, target_directed_edges, degree_model, gamma, max_deg, seed, permute, 0, -1, out, n_padded, nnz);
+}
+
+int mggcn_gen_rows_begin(int64_t n_raw, int64_t target_directed_edges, int degree_model, double gamma,
+                         int64_t max_deg, uint64_t seed, int permute, int64_t row_begin, int64_t row_end,
+                         mggcn_gen_t **out, int64_t *n_padded, int64_t *nnz_rows) {
+    if (row_end < 0) return fail(MGGCN_E_INVALID, "negative row range");
+    return gen_rows(n_raw, target_directed_edges, degree_model, gamma, max_deg, seed, permute, row_begin, row_end, out,
+                    n_padded, nnz_rows);
 }
 
 int mggcn_gen_graph_finish(mggcn_gen_t *g, uint64_t *rowptr, uint32_t *colidx, float *vals) {
@@ -220,6 +245,51 @@ int mggcn_gen_features(int64_t n_raw, int64_t n_padded, int64_t f_raw, int64_t f
             else
                 row[j] = 0.f;
         }
+    }
+    return MGGCN_OK;
+}
+
+// Rows [r0, r1) of what mggcn_gen_features / mggcn_gen_labels produce (out holds r1 - r0 rows).
+int mggcn_gen_features_rows(int64_t n_raw, int64_t n_padded, int64_t f_raw, int64_t f_padded, uint64_t seed,
+                            int permute, int64_t row_begin, int64_t row_end, float *out) {
+    if (!out || n_raw > n_padded || f_raw > f_padded || row_begin < 0 || row_begin > row_end || row_end > n_padded)
+        return fail(MGGCN_E_INVALID, "bad argument");
+    std::vector<uint32_t> inv;  // old id of a new (permuted) id
+    if (permute) {
+        const std::vector<uint32_t> perm = make_perm(n_padded, seed ? seed : 1);
+        inv.resize((size_t)n_padded);
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n_padded; ++i) inv[perm[i]] = (uint32_t)i;
+    }
+#pragma omp parallel for schedule(static)
+    for (int64_t r = row_begin; r < row_end; ++r) {
+        const int64_t i = permute ? (int64_t)inv[r] : r;
+        float *row = out + (size_t)(r - row_begin) * f_padded;
+        for (int64_t j = 0; j < f_padded; ++j) {
+            if (i < n_raw && j < f_raw)
+                row[j] = (float)(2.0 * u01(hash2(seed ^ 0x46454154ull, (uint64_t)i * f_raw + j)) - 1.0);
+            else
+                row[j] = 0.f;
+        }
+    }
+    return MGGCN_OK;
+}
+
+int mggcn_gen_labels_rows(int64_t n_raw, int64_t n_padded, int num_classes, uint64_t seed, int permute,
+                          int64_t row_begin, int64_t row_end, int32_t *out) {
+    if (!out || n_raw > n_padded || num_classes <= 0 || row_begin < 0 || row_begin > row_end || row_end > n_padded)
+        return fail(MGGCN_E_INVALID, "bad argument");
+    std::vector<uint32_t> inv;
+    if (permute) {
+        const std::vector<uint32_t> perm = make_perm(n_padded, seed ? seed : 1);
+        inv.resize((size_t)n_padded);
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n_padded; ++i) inv[perm[i]] = (uint32_t)i;
+    }
+#pragma omp parallel for schedule(static)
+    for (int64_t r = row_begin; r < row_end; ++r) {
+        const int64_t i = permute ? (int64_t)inv[r] : r;
+        out[r - row_begin] = i < n_raw ? (int32_t)(hash2(seed ^ 0x4C41424Cull, (uint64_t)i) % (uint64_t)num_classes) : 0;
     }
     return MGGCN_OK;
 }

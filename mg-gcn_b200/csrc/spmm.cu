@@ -31,6 +31,7 @@ using namespace mggcn;
 
 namespace mggcn {
 extern int g_gemm_tc, g_gemm_kgroup;  // gemm_tc.cu
+extern int g_skip_exchange;           // engine.cu
 }
 
 namespace {
@@ -46,13 +47,23 @@ struct split_row {
 
 }  // namespace
 
+// One launch worth of work: items [first_item, first_item + n_items) of the plan's list; the first n_seg of them
+// are segments of split rows (segment k writes partial slot k), rows [first_split, first_split + n_split) of the
+// split list are finished by the fix-up kernel.
+struct plan_block {
+    int64_t first_item = 0, n_items = 0, n_seg = 0, first_split = 0, n_split = 0;
+};
+
 struct mggcn_spmm_plan {
     int64_t rows = 0;
-    int64_t n_items = 0;  // segments + whole rows
-    int64_t n_seg = 0;    // items [0, n_seg) are segments; item k writes partial slot k
-    int64_t n_split_rows = 0;
     int split_nnz = 0;
     int device = 0;
+    // blk.size() == 1: the whole matrix in one launch.  > 1: column blocks (2-D schedule, see plan_create_blocked):
+    // block j holds, per row, the entries whose column falls into the j-th range of `blk_cols` columns; the blocks
+    // are multiplied one after the other (and per feature window) so that the rows of B a launch gathers stay in L2.
+    std::vector<plan_block> blk;
+    int64_t blk_cols = 0;   // columns per block (the last one may be smaller)
+    int64_t max_seg = 0;    // max over blocks of n_seg (workspace slots)
     spmm_item *d_items = nullptr;
     split_row *d_split = nullptr;
 };
@@ -64,7 +75,10 @@ int g_threads = 64;   // CTA size
 int g_policy = 1;     // 1: L2 evict_last for B, evict_first for the CSR stream; 0: plain loads
 int g_split = 0;      // row-split threshold of new plans; 0 = chosen from the matrix (see plan_create)
 int g_slices = 0;     // k > 1: run as k launches over F/k-wide column windows of B and C; 0: k = 2 when B (cols x F floats)
-                      // is larger than half of the L2 but its half is not (see spmm_sliced); 1: never
+                      // is larger than half of the L2 but its half is not (see spmm_scheduled); 1: never
+int g_blocks = 0;     // column blocks of new blocked plans: 0 = from the traffic model, 1 = never, k = exactly k
+int g_window = 0;     // feature-window width of blocked plans at launch: 0 = widest that keeps a block's B rows resident
+int g_tile_mb = 0;    // bytes of B a launch may count on staying L2-resident, in MiB; 0 = 45 % of the L2
 
 struct spmm_args {
     const spmm_item *items;  // null: natural order, one item per row from rowptr
@@ -430,6 +444,8 @@ __global__ void spmm_fixup_kernel(const split_row *rows, int64_t n_split, const 
     }
 }
 
+thread_local char t_last_config[256] = "";
+
 template <int LANES, int NCH, int VEC>
 int launch_cfg(cudaStream_t st, const spmm_args &a) {
     constexpr int GROUPS = 32 / LANES;
@@ -441,10 +457,12 @@ int launch_cfg(cudaStream_t st, const spmm_args &a) {
     constexpr int U4 = LANES < 4 ? LANES : 4;
     const bool exact = a.F % (LANES * NCH * VEC) == 0;
     const unsigned gr = (unsigned)grid;
+    int unroll = U4;
     if (a.g.flags) {  // gathered multi-GPU operand
         if (exact) spmm_kernel<LANES, NCH, VEC, U4, true, true><<<gr, threads, 0, st>>>(a);
         else spmm_kernel<LANES, NCH, VEC, U4, false, true><<<gr, threads, 0, st>>>(a);
     } else if (g_unroll >= 8 && LANES >= 8) {
+        unroll = 8;
         if (exact) spmm_kernel<LANES, NCH, VEC, 8, true><<<gr, threads, 0, st>>>(a);
         else spmm_kernel<LANES, NCH, VEC, 8, false><<<gr, threads, 0, st>>>(a);
     } else {
@@ -452,13 +470,17 @@ int launch_cfg(cudaStream_t st, const spmm_args &a) {
         else spmm_kernel<LANES, NCH, VEC, U4, false><<<gr, threads, 0, st>>>(a);
     }
     MGGCN_LAUNCH_CHECK();
+    snprintf(t_last_config, sizeof t_last_config, "spmm_kernel<%d,%d,%d,%d,%s%s> grid=%u cta=%d F=%d", LANES, NCH, VEC, unroll,
+             exact ? "exact" : "ragged", a.g.flags ? ",gathered" : "", gr, threads, a.F);
     return MGGCN_OK;
 }
 
+// One launch (+ fix-up of its split rows): the whole matrix (plan == null: natural row order), or block `pb` of a plan.
 int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowptr, int rowptr64,
                   const uint32_t *colidx, const float *vals, const float *B, int64_t ldb, float *C,
                   int64_t ldc, int F, float alpha, float beta, const mggcn_epilogue *epi,
-                  const mggcn_spmm_plan_t *plan, void *ws, const mggcn::spmm_gather *gather = nullptr) {
+                  const mggcn_spmm_plan_t *plan, const plan_block *pb, void *ws,
+                  const mggcn::spmm_gather *gather = nullptr) {
     if (rows < 0 || cols < 0 || F < 0) return fail(MGGCN_E_INVALID, "negative dimension");
     if (rows == 0 || F == 0) return MGGCN_OK;
     if (!rowptr && !plan) return fail(MGGCN_E_INVALID, "rowptr is null");
@@ -467,10 +489,11 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
     if (rows > 0xFFFFFFFFll) return fail(MGGCN_E_UNSUPPORTED, "more than 2^32 rows in one block");
     if (plan && plan->rows != rows) return fail(MGGCN_E_INVALID, "plan was built for %lld rows, got %lld",
                                                (long long)plan->rows, (long long)rows);
+    if (plan && !pb) pb = &plan->blk[0];
     spmm_args a{};
-    a.items = plan ? plan->d_items : nullptr;
-    a.n_items = plan ? plan->n_items : rows;
-    a.n_seg = plan ? plan->n_seg : 0;
+    a.items = plan ? plan->d_items + pb->first_item : nullptr;
+    a.n_items = plan ? pb->n_items : rows;
+    a.n_seg = plan ? pb->n_seg : 0;
     a.rowptr = rowptr;
     a.rowptr64 = rowptr64;
     a.colidx = colidx;
@@ -526,10 +549,10 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
         else rc = launch_cfg<32, 4, 1>(st, a);
     }
     if (rc) return rc;
-    if (plan && plan->n_split_rows > 0) {
-        const int64_t total = plan->n_split_rows * (int64_t)F;
+    if (plan && pb->n_split > 0) {
+        const int64_t total = pb->n_split * (int64_t)F;
         const int grid = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
-        spmm_fixup_kernel<<<grid, 256, 0, st>>>(plan->d_split, plan->n_split_rows, a.partial, a.ldp, C,
+        spmm_fixup_kernel<<<grid, 256, 0, st>>>(plan->d_split + pb->first_split, pb->n_split, a.partial, a.ldp, C,
                                                 ldc, F, alpha, beta, a.epi);
         MGGCN_LAUNCH_CHECK();
     }
@@ -538,96 +561,135 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
 
 thread_local int64_t t_touched_cols = -1;
 
-// Feature slicing: k launches over F/k-wide column windows (every window a multiple of 4 floats, >= 32 wide).
-int spmm_sliced(cudaStream_t st, int64_t rows, int64_t cols, const void *rowptr, int rowptr64, const uint32_t *colidx,
-                const float *vals, const float *B, int64_t ldb, float *C, int64_t ldc, int F, float alpha, float beta,
-                const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws) {
-    // Why: B is the operand with reuse, and the two L2 halves of the chip each keep their own copy of a line, so
-    // B stays resident only up to about half of the 126 MB.  At reddit shape (119 MB at F = 128) the unsliced
-    // kernel re-reads B from DRAM 9 times over (10.7 GB per launch); it is not DRAM-bound, but inside a training
-    // loop the board runs at its power cap and the DRAM traffic costs SM clock: two 64-wide windows measured
-    // 21.3 ms/epoch at 1.78 GHz against 23.2 ms at 1.60 GHz.  The sums per output element are the same either way.
-    // At 2 GPUs (blocks of 60 MB) slicing costs 2.5 % instead; the crossover between 60 and 119 MB has not been
-    // measured, so the rule only fires from 90 MB (midpoint) up to the L2 size.  Callers whose CSR
-    // touches only part of B's rows (the engine's grouped launches) say so through spmm_touched_cols_hint.
-    int k = g_slices;
-    if (k == 0) {
+// What a launch can keep resident of the operand with reuse (B): the two L2 halves of the chip each cache the
+// lines the SMs of their die ask for, so a B that every SM gathers from stays resident only up to about half of
+// the L2 (measured on B200: 60 MB windows hit 88 %, a 119 MB B is re-read from DRAM 9 times over).
+int64_t l2_bytes() {
+    static int64_t v = [] {
+        int dev = 0, l2 = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, dev) != cudaSuccess || l2 <= 0) {
+            cudaGetLastError();
+            l2 = 126 << 20;
+        }
+        return (int64_t)l2;
+    }();
+    return v;
+}
+int64_t resident_budget() { return g_tile_mb > 0 ? (int64_t)g_tile_mb << 20 : l2_bytes() * 45 / 100; }
+
+// The schedule of one product: feature windows x column blocks.
+//   * Column blocks come from the plan (plan_create_blocked): launches walk block after block, C accumulates with
+//     beta = 1 between them, the caller's beta belongs to the first block and the epilogue to the last (their item
+//     lists cover every row; the blocks in between list only rows that have entries there).
+//   * Feature windows: w floats of every row of B and C per pass, chosen so that (columns of a block) x w x 4 bytes
+//     stays L2-resident.  Without column blocks this is the feature slicing of round 1: two windows when B is between
+//     ~0.7 and 1 L2 (reddit shape, F = 128: 4.4 GB of DRAM traffic per aggregation instead of 10.7).
+// The sums per output element are taken block by block in column order: deterministic, and equal to the unblocked
+// order up to fp32 rounding of the partial sums (inside the 1e-5 bar, tests/test_gpu_spmm.py).
+int spmm_scheduled(cudaStream_t st, int64_t rows, int64_t cols, const void *rowptr, int rowptr64, const uint32_t *colidx,
+                   const float *vals, const float *B, int64_t ldb, float *C, int64_t ldc, int F, float alpha, float beta,
+                   const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws) {
+    const int nblk = plan ? (int)plan->blk.size() : 1;
+    int w = F;
+    if (nblk > 1) {
+        const int64_t budget = resident_budget();
+        w = 256;
+        while (w > 32 && plan->blk_cols * (int64_t)w * 4 > budget) w /= 2;
+        if (g_window > 0) w = g_window;
+        if (w > F) w = F;
+    } else if (g_slices > 1) {
+        if (F % (4 * g_slices) == 0 && F / g_slices >= 32) w = F / g_slices;
+    } else if (g_slices == 0) {
         const double bytes = (double)(t_touched_cols >= 0 ? t_touched_cols : cols) * (double)F * 4.0;
-        k = (bytes > 90e6 && bytes <= 124e6 && F % 8 == 0 && F / 2 >= 64) ? 2 : 1;
+        const double l2 = (double)l2_bytes();
+        if (bytes > 0.68 * l2 && bytes <= 0.94 * l2 && F % 8 == 0 && F / 2 >= 64) w = F / 2;
     }
-    if (k <= 1 || F % (4 * k) != 0 || F / k < 32)
-        return spmm_dispatch(st, rows, cols, rowptr, rowptr64, colidx, vals, B, ldb, C, ldc, F, alpha, beta, epi, plan, ws);
-    const int w = F / k;
-    for (int i = 0; i < k; ++i) {
+    if (w % 4 != 0 && w != F) w = (w + 3) / 4 * 4;
+    if (nblk == 1 && w >= F)
+        return spmm_dispatch(st, rows, cols, rowptr, rowptr64, colidx, vals, B, ldb, C, ldc, F, alpha, beta, epi, plan, nullptr, ws);
+    int nwin = 0;
+    char first[sizeof t_last_config];
+    for (int f0 = 0; f0 < F; f0 += w, ++nwin) {
+        const int fw = std::min(w, F - f0);
         mggcn_epilogue e2{};
         if (epi) {
             e2 = *epi;
-            if (e2.bias) e2.bias += i * w;
-            if (e2.aux) e2.aux += i * w;
-            if (e2.keep_mask) e2.keep_mask += i * w;
+            if (e2.bias) e2.bias += f0;
+            if (e2.aux) e2.aux += f0;
+            if (e2.keep_mask) e2.keep_mask += f0;
         }
-        const int rc = spmm_dispatch(st, rows, cols, rowptr, rowptr64, colidx, vals, B + i * w, ldb, C + i * w, ldc, w, alpha,
-                                     beta, epi ? &e2 : nullptr, plan, ws);
-        if (rc) return rc;
+        for (int j = 0; j < nblk; ++j) {
+            const bool last = j == nblk - 1;
+            const int rc = spmm_dispatch(st, rows, cols, rowptr, rowptr64, colidx, vals, B + f0, ldb, C + f0, ldc, fw, alpha,
+                                         j == 0 ? beta : 1.f, last && epi ? &e2 : nullptr, plan, plan ? &plan->blk[j] : nullptr, ws);
+            if (rc) return rc;
+            if (nwin == 0 && j == 0) memcpy(first, t_last_config, sizeof first);
+        }
     }
+    char tmp[sizeof t_last_config];
+    snprintf(tmp, sizeof tmp, "%.150s x %d feature window(s) of %d x %d column block(s) of %lld", first, nwin, w, nblk,
+             (long long)(plan && nblk > 1 ? plan->blk_cols : cols));
+    memcpy(t_last_config, tmp, sizeof tmp);
     return MGGCN_OK;
 }
 
-template <typename idx_t>
-int plan_create(int64_t rows, const idx_t *rowptr, int split_nnz, mggcn_spmm_plan_t **out) {
-    if (!out || rows < 0 || (rows > 0 && !rowptr)) return fail(MGGCN_E_INVALID, "bad argument");
-    if (rows > 0xFFFFFFFFll) return fail(MGGCN_E_UNSUPPORTED, "more than 2^32 rows in one block");
+int pick_split(uint64_t nnz, int split_nnz) {
     if (split_nnz <= 0) split_nnz = g_split;
     if (split_nnz <= 0) {
         // A warp works through its item with a fixed number of gathers in flight, so one long item
         // is a serial chain of L2 round trips: keep every item well below the kernel's duration.
         // Aim at >= 2 items per resident warp slot (148 SMs x 32 warps), between 64 and 2048 entries
         // (measured on B200: reddit-shape whole matrix best at 2048, its 8x8 blocks at 256-512).
-        const uint64_t nnz = rows > 0 ? (uint64_t)rowptr[rows] - (uint64_t)rowptr[0] : 0;
         uint64_t s = nnz / (148ull * 32 * 2);
         s = (s + 31) / 32 * 32;
         split_nnz = (int)std::min<uint64_t>(2048, std::max<uint64_t>(64, s));
     }
-    if (split_nnz < 32) split_nnz = 32;
-    auto *p = new (std::nothrow) mggcn_spmm_plan;
-    if (!p) return fail(MGGCN_E_NOMEM, "out of memory");
-    p->rows = rows;
-    p->split_nnz = split_nnz;
+    return std::max(split_nnz, 32);
+}
 
-    // whole rows, longest first (counting sort on the length: stable, O(rows))
-    std::vector<uint32_t> order;
-    std::vector<spmm_item> items;
-    std::vector<split_row> split;
+// Appends one launch worth of items to `items` / `split`: rows r in [0, rows) with entries [beg(r), beg(r) + len(r));
+// rows without entries are listed only when keep_empty.  Rows longer than split_nnz become equal segments (listed
+// first), whole rows follow longest-first (counting sort on the length: stable, O(rows)).
+template <typename beg_fn, typename len_fn>
+plan_block build_block(int64_t rows, int split_nnz, bool keep_empty, beg_fn beg, len_fn len, std::vector<spmm_item> &items,
+                       std::vector<split_row> &split) {
+    plan_block pb;
+    pb.first_item = (int64_t)items.size();
+    pb.first_split = (int64_t)split.size();
     std::vector<uint32_t> whole;
     whole.reserve((size_t)rows);
     for (int64_t r = 0; r < rows; ++r) {
-        const uint64_t len = (uint64_t)rowptr[r + 1] - (uint64_t)rowptr[r];
-        if (len > (uint64_t)split_nnz) {
-            const uint64_t nseg = (len + split_nnz - 1) / split_nnz;
-            const uint64_t seg = (len + nseg - 1) / nseg;
-            split.push_back({(uint32_t)r, (uint32_t)items.size(), (uint32_t)nseg});
+        const uint64_t l = len(r);
+        if (l > (uint64_t)split_nnz) {
+            const uint64_t nseg = (l + split_nnz - 1) / split_nnz;
+            const uint64_t seg = (l + nseg - 1) / nseg;
+            split.push_back({(uint32_t)r, (uint32_t)(items.size() - (size_t)pb.first_item), (uint32_t)nseg});
             for (uint64_t k = 0; k < nseg; ++k) {
-                const uint64_t b = k * seg, e = std::min(len, b + seg);
-                items.push_back({(uint64_t)rowptr[r] + b, (uint32_t)(e - b), (uint32_t)r});
+                const uint64_t b = k * seg, e = std::min(l, b + seg);
+                items.push_back({beg(r) + b, (uint32_t)(e - b), (uint32_t)r});
             }
-        } else {
+        } else if (l > 0 || keep_empty) {
             whole.push_back((uint32_t)r);
         }
     }
-    p->n_seg = (int64_t)items.size();
-    p->n_split_rows = (int64_t)split.size();
-    {
-        std::vector<uint64_t> hist((size_t)split_nnz + 2, 0);
-        for (uint32_t r : whole) hist[(size_t)split_nnz - (size_t)(rowptr[r + 1] - rowptr[r]) + 1]++;
-        for (size_t i = 1; i < hist.size(); ++i) hist[i] += hist[i - 1];
-        const size_t base = items.size();
-        items.resize(base + whole.size());
-        for (uint32_t r : whole) {
-            const uint64_t len = (uint64_t)rowptr[r + 1] - (uint64_t)rowptr[r];
-            items[base + hist[(size_t)split_nnz - (size_t)len]++] = {(uint64_t)rowptr[r], (uint32_t)len, r};
-        }
+    pb.n_seg = (int64_t)items.size() - pb.first_item;
+    pb.n_split = (int64_t)split.size() - pb.first_split;
+    std::vector<uint64_t> hist((size_t)split_nnz + 2, 0);
+    for (uint32_t r : whole) hist[(size_t)split_nnz - (size_t)len(r) + 1]++;
+    for (size_t i = 1; i < hist.size(); ++i) hist[i] += hist[i - 1];
+    const size_t base = items.size();
+    items.resize(base + whole.size());
+    for (uint32_t r : whole) {
+        const uint64_t l = len(r);
+        items[base + hist[(size_t)split_nnz - (size_t)l]++] = {beg(r), (uint32_t)l, r};
     }
-    p->n_items = (int64_t)items.size();
+    pb.n_items = (int64_t)items.size() - pb.first_item;
+    return pb;
+}
+
+int plan_upload(mggcn_spmm_plan *p, const std::vector<spmm_item> &items, const std::vector<split_row> &split,
+                mggcn_spmm_plan_t **out) {
+    for (const plan_block &b : p->blk) p->max_seg = std::max(p->max_seg, b.n_seg);
     cudaError_t e = cudaGetDevice(&p->device);
     if (e == cudaSuccess && !items.empty()) e = cudaMalloc(&p->d_items, items.size() * sizeof(spmm_item));
     if (e == cudaSuccess && !items.empty())
@@ -645,6 +707,105 @@ int plan_create(int64_t rows, const idx_t *rowptr, int split_nnz, mggcn_spmm_pla
     return MGGCN_OK;
 }
 
+template <typename idx_t>
+int plan_create(int64_t rows, const idx_t *rowptr, int split_nnz, mggcn_spmm_plan_t **out) {
+    if (!out || rows < 0 || (rows > 0 && !rowptr)) return fail(MGGCN_E_INVALID, "bad argument");
+    if (rows > 0xFFFFFFFFll) return fail(MGGCN_E_UNSUPPORTED, "more than 2^32 rows in one block");
+    split_nnz = pick_split(rows > 0 ? (uint64_t)rowptr[rows] - (uint64_t)rowptr[0] : 0, split_nnz);
+    auto *p = new (std::nothrow) mggcn_spmm_plan;
+    if (!p) return fail(MGGCN_E_NOMEM, "out of memory");
+    p->rows = rows;
+    p->split_nnz = split_nnz;
+    std::vector<spmm_item> items;
+    std::vector<split_row> split;
+    p->blk.push_back(build_block(rows, split_nnz, true, [&](int64_t r) { return (uint64_t)rowptr[r]; },
+                                 [&](int64_t r) { return (uint64_t)rowptr[r + 1] - (uint64_t)rowptr[r]; }, items, split));
+    return plan_upload(p, items, split, out);
+}
+
+// DRAM bytes one product of width F is expected to move under a schedule of nblk column blocks (nblk = 1: none).
+// Unblocked, a B larger than what stays resident misses on (1 - resident / B) of its gathers, each a sector read of
+// the row slice; blocked, B is read once, the CSR stream once per feature window, and C once per block and window.
+double schedule_cost(double rows, double cols, double nnz, int F, int nblk, double budget) {
+    const double Fb = F * 4.0, Bbytes = cols * Fb;
+    if (nblk <= 1) {
+        const double miss = Bbytes <= budget ? 0.0 : 1.0 - budget / Bbytes;
+        return nnz * 8.0 + Bbytes + nnz * Fb * miss + rows * Fb;
+    }
+    int w = 256;
+    const double bc = std::ceil(cols / nblk);
+    while (w > 32 && bc * w * 4.0 > budget) w /= 2;
+    w = std::min(w, F);
+    const double nwin = std::ceil((double)F / w);
+    const double item_rows = rows * (2.0 + (nblk - 2) * std::min(1.0, nnz / rows / nblk));  // first and last list every row
+    return nwin * (nnz * 8.0 + item_rows * 16.0) + Bbytes + rows * Fb * (2.0 * nblk - 1.0);
+}
+
+// Column-blocked plan.  Rows store their columns ascending in key(c) = (c - col_rot) mod cols (col_rot = 0: plain
+// ascending CSR; the engine's grouped operands store stage blocks cyclically), so the entries of a row that fall
+// into one column block are contiguous and a block is just another item list over the same colidx / vals arrays.
+int plan_create_blocked(int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx, uint32_t col_rot,
+                        int64_t col_span, int F_hint, int split_nnz, mggcn_spmm_plan_t **out) {
+    if (!out || rows < 0 || cols < 0 || (rows > 0 && !rowptr)) return fail(MGGCN_E_INVALID, "bad argument");
+    if (cols == 0 || !colidx) return plan_create<uint32_t>(rows, rowptr, split_nnz, out);
+    if (col_span <= 0 || col_span > cols) col_span = cols;
+    const uint64_t nnz = rows > 0 ? (uint64_t)rowptr[rows] : 0;
+    int nblk = g_blocks;
+    if (nblk <= 0) {
+        // choose the block count that the traffic model likes best; blocks only pay when B is far beyond the L2
+        const double budget = (double)resident_budget();
+        nblk = 1;
+        double best = schedule_cost((double)rows, (double)col_span, (double)nnz, F_hint, 1, budget);
+        for (int w = 32; w <= 128; w *= 2) {
+            const int q = (int)std::ceil((double)col_span * w * 4.0 / budget);
+            if (q < 2 || q > 64) continue;
+            const double c = schedule_cost((double)rows, (double)col_span, (double)nnz, F_hint, q, budget);
+            if (c < 0.8 * best) { best = c; nblk = q; }
+        }
+    }
+    if (nblk <= 1 || rows == 0) return plan_create<uint32_t>(rows, rowptr, split_nnz, out);
+    if (rows > 0xFFFFFFFFll) return fail(MGGCN_E_UNSUPPORTED, "more than 2^32 rows in one block");
+    auto *p = new (std::nothrow) mggcn_spmm_plan;
+    if (!p) return fail(MGGCN_E_NOMEM, "out of memory");
+    p->rows = rows;
+    p->blk_cols = (col_span + nblk - 1) / nblk;
+    p->split_nnz = split_nnz = pick_split(nnz / (uint64_t)nblk, split_nnz);
+    // ptr[r * (nblk + 1) + j] = first entry of row r whose key is >= j * blk_cols
+    std::vector<uint32_t> ptr((size_t)rows * (size_t)(nblk + 1));
+    const uint32_t ucols = (uint32_t)cols;
+    int bad = 0;
+#pragma omp parallel for schedule(static) reduction(max : bad)
+    for (int64_t r = 0; r < rows; ++r) {
+        uint32_t *pr = ptr.data() + (size_t)r * (size_t)(nblk + 1);
+        const uint32_t end = rowptr[r + 1];
+        uint64_t prev = 0;
+        int j = 0;
+        pr[0] = rowptr[r];
+        for (uint32_t k = rowptr[r]; k < end; ++k) {
+            const uint32_t c = colidx[k];
+            const uint64_t key = c >= col_rot ? c - col_rot : (uint64_t)c + ucols - col_rot;
+            if (key < prev || key >= (uint64_t)col_span) bad = 1;  // not ascending in the rotated order / outside the span
+            prev = key;
+            while (j + 1 < nblk && key >= (uint64_t)(j + 1) * (uint64_t)p->blk_cols) pr[++j] = k;
+        }
+        while (j < nblk) pr[++j] = end;
+    }
+    if (bad) {
+        delete p;
+        return fail(MGGCN_E_INVALID, "rows are not sorted by column (rotated by %u) or reach beyond the column span", col_rot);
+    }
+    std::vector<spmm_item> items;
+    std::vector<split_row> split;
+    for (int j = 0; j < nblk; ++j) {
+        const size_t st = (size_t)(nblk + 1);
+        p->blk.push_back(build_block(rows, split_nnz, j == 0 || j == nblk - 1,
+                                     [&](int64_t r) { return (uint64_t)ptr[(size_t)r * st + j]; },
+                                     [&](int64_t r) { return (uint64_t)(ptr[(size_t)r * st + j + 1] - ptr[(size_t)r * st + j]); }, items,
+                                     split));
+    }
+    return plan_upload(p, items, split, out);
+}
+
 }  // namespace
 
 namespace mggcn {
@@ -654,7 +815,8 @@ void spmm_touched_cols_hint(int64_t n) { t_touched_cols = n; }
 int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx,
                   const float *vals, float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
                   float beta, const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws, const spmm_gather &g) {
-    return spmm_dispatch(st, rows, cols, rowptr, 0, colidx, vals, gathered, ld, C, ldc, F, alpha, beta, epi, plan, ws, &g);
+    if (plan && plan->blk.size() != 1) return fail(MGGCN_E_INVALID, "the gathered form takes an unblocked plan");
+    return spmm_dispatch(st, rows, cols, rowptr, 0, colidx, vals, gathered, ld, C, ldc, F, alpha, beta, epi, plan, nullptr, ws, &g);
 }
 }  // namespace mggcn
 
@@ -666,6 +828,7 @@ int mggcn_spmm_gathered_f32_i32(mggcn_stream_t stream, int64_t rows, int64_t col
                                 const uint32_t *cuts, const uint32_t *stage_flags, int *err,
                                 const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws) {
     if (!cuts || P < 1 || P > 16 || rank < 0 || rank >= P) return fail(MGGCN_E_INVALID, "bad partition description");
+    if (plan && plan->blk.size() != 1) return fail(MGGCN_E_INVALID, "the gathered form takes an unblocked plan");
     mggcn::spmm_gather g;
     g.flags = stage_flags;
     g.B_own = B_own;
@@ -676,23 +839,23 @@ int mggcn_spmm_gathered_f32_i32(mggcn_stream_t stream, int64_t rows, int64_t col
     g.err = err;
     for (int i = 0; i < 16; ++i) g.cuts[i] = i < P ? cuts[i] : 0xFFFFFFFFu;
     return spmm_dispatch(static_cast<cudaStream_t>(stream), rows, cols, rowptr, 0, colidx, vals, gathered, ld, C, ldc, F,
-                         alpha, beta, epi, plan, ws, &g);
+                         alpha, beta, epi, plan, nullptr, ws, &g);
 }
 
 int mggcn_spmm_csr_f32_i32(mggcn_stream_t stream, int64_t rows, int64_t cols, const uint32_t *rowptr,
                            const uint32_t *colidx, const float *vals, const float *B, int64_t ldb,
                            float *C, int64_t ldc, int F, float alpha, float beta,
                            const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws) {
-    return spmm_sliced(static_cast<cudaStream_t>(stream), rows, cols, rowptr, 0, colidx, vals, B, ldb,
-                       C, ldc, F, alpha, beta, epi, plan, ws);
+    return spmm_scheduled(static_cast<cudaStream_t>(stream), rows, cols, rowptr, 0, colidx, vals, B, ldb,
+                          C, ldc, F, alpha, beta, epi, plan, ws);
 }
 
 int mggcn_spmm_csr_f32_i64(mggcn_stream_t stream, int64_t rows, int64_t cols, const uint64_t *rowptr,
                            const uint32_t *colidx, const float *vals, const float *B, int64_t ldb,
                            float *C, int64_t ldc, int F, float alpha, float beta,
                            const mggcn_epilogue *epi, const mggcn_spmm_plan_t *plan, void *ws) {
-    return spmm_sliced(static_cast<cudaStream_t>(stream), rows, cols, rowptr, 1, colidx, vals, B, ldb,
-                       C, ldc, F, alpha, beta, epi, plan, ws);
+    return spmm_scheduled(static_cast<cudaStream_t>(stream), rows, cols, rowptr, 1, colidx, vals, B, ldb,
+                          C, ldc, F, alpha, beta, epi, plan, ws);
 }
 
 int mggcn_spmm_plan_create_i32(int64_t rows, const uint32_t *rowptr_host, int split_nnz,
@@ -703,11 +866,17 @@ int mggcn_spmm_plan_create_i64(int64_t rows, const uint64_t *rowptr_host, int sp
                                mggcn_spmm_plan_t **out) {
     return plan_create<uint64_t>(rows, rowptr_host, split_nnz, out);
 }
+int mggcn_spmm_plan_create_blocked_i32(int64_t rows, int64_t cols, const uint32_t *rowptr_host,
+                                       const uint32_t *colidx_host, uint32_t col_rot, int64_t col_span, int F_hint,
+                                       int split_nnz, mggcn_spmm_plan_t **out) {
+    return plan_create_blocked(rows, cols, rowptr_host, colidx_host, col_rot, col_span, F_hint, split_nnz, out);
+}
 
 size_t mggcn_spmm_plan_workspace_bytes(const mggcn_spmm_plan_t *plan, int F) {
     if (!plan || F <= 0) return 0;
-    return (size_t)plan->n_seg * (size_t)((F + 3) / 4 * 4) * sizeof(float);
+    return (size_t)plan->max_seg * (size_t)((F + 3) / 4 * 4) * sizeof(float);
 }
+int mggcn_spmm_plan_blocks(const mggcn_spmm_plan_t *plan) { return plan ? (int)plan->blk.size() : 0; }
 
 void mggcn_spmm_plan_destroy(mggcn_spmm_plan_t *plan) {
     if (!plan) return;
@@ -715,6 +884,8 @@ void mggcn_spmm_plan_destroy(mggcn_spmm_plan_t *plan) {
     if (plan->d_split) cudaFree(plan->d_split);
     delete plan;
 }
+
+const char *mggcn_last_spmm_config(void) { return t_last_config; }
 
 int mggcn_tune(const char *key, int value) {
     if (!key) return MGGCN_E_INVALID;
@@ -724,8 +895,12 @@ int mggcn_tune(const char *key, int value) {
     else if (!strcmp(key, "policy")) slot = &g_policy;
     else if (!strcmp(key, "split")) slot = &g_split;
     else if (!strcmp(key, "slices")) slot = &g_slices;
+    else if (!strcmp(key, "blocks")) slot = &g_blocks;
+    else if (!strcmp(key, "window")) slot = &g_window;
+    else if (!strcmp(key, "tile_mb")) slot = &g_tile_mb;
     else if (!strcmp(key, "gemm_tc")) slot = &mggcn::g_gemm_tc;
     else if (!strcmp(key, "gemm_kgroup")) slot = &mggcn::g_gemm_kgroup;
+    else if (!strcmp(key, "skip_exchange")) slot = &mggcn::g_skip_exchange;
     if (!slot) return fail(MGGCN_E_INVALID, "unknown tuning key %s", key);
     const int old = *slot;
     if (slot == &g_threads && (value < 32 || value > 256 || value % 32)) return fail(MGGCN_E_INVALID, "threads must be 32..256");

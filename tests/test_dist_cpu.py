@@ -51,6 +51,23 @@ def _worker(rank, world, port, q):
         parts = [torch.empty((int(cuts[r + 1] - cuts[r]), F)) for r in range(world)]
         dist.all_gather(parts, t) if len({p.shape for p in parts}) == 1 else None
         assert mg.pad_classes(C, world) % world == 0
+        # 5. sharded pre-processing (bench.py's path): the rank generates only its row slab, the degrees travel
+        # through all_gather, and the blocks it derives are bit-identical to normalise -> transpose -> split of
+        # the whole graph -- no rank ever holds more than its slab
+        shape = (1500, 1500 * 14, 20, 5, 1, 2.5, 200)
+        slab, Xl, Yl, _ = mg.generate_rows(shape, r0, r1, seed=3)
+        assert np.array_equal(Xl, X[r0:r1]) and np.array_equal(Yl, Y[r0:r1])
+        dl = torch.from_numpy(np.diff(slab.rowptr.astype(np.int64)).astype(np.int32))
+        dparts = [torch.empty(int(cuts[r + 1] - cuts[r]), dtype=torch.int32) for r in range(world)]
+        dist.all_gather(dparts, dl)
+        deg_all = torch.cat(dparts).numpy().astype(np.uint32)
+        fwd, bwd = mg.slab_operands(slab, deg_all, r0)
+        local = np.array([0, slab.n], np.uint32)
+        for mine_b, want_b in ((fwd.block_rows(local, cuts, only_row=0), blocks),
+                               (bwd.block_rows(local, cuts, only_row=0), A.block_rows(cuts, cuts, only_row=rank))):
+            for a, b in zip(mine_b, want_b):
+                assert np.array_equal(a.rowptr, b.rowptr) and np.array_equal(a.colidx, b.colidx)
+                assert np.array_equal(a.vals.view(np.uint32), b.vals.view(np.uint32))
         q.put((rank, "ok"))
     except Exception as e:  # noqa: BLE001
         q.put((rank, repr(e)))

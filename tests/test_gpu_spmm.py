@@ -279,3 +279,99 @@ def test_gathered_block_row_matches_oracle(mg, orc, cuda, F, late, P, rank):
     got = Cm.cpu().numpy()[:, :F]
     assert np.isfinite(got).all()
     check(got, want, scale)
+
+
+@pytest.mark.parametrize("F,ld", [(256, 256), (128, 128), (47, 48), (100, 104), (8, 8)])
+@pytest.mark.parametrize("nblk,rot", [(2, 0), (5, 0), (7, 811), (3, 1299)])
+def test_column_blocked_plan_matches_oracle(mg, orc, cuda, F, ld, nblk, rot):
+    """2-D schedule (mggcn_spmm_plan_create_blocked_i32): feature windows x column blocks over the same CSR arrays,
+    C accumulated between blocks, caller's beta on the first block and the epilogue on the last.  Rows carry an
+    empty row, hub rows that are split inside a block, and (rot != 0) columns stored in rotated order like the
+    engine's grouped operands."""
+    torch = cuda
+    rng = np.random.default_rng(F + nblk)
+    n, m = 1700, 1300
+    rp, ci, va = random_csr(rng, n, m, 30, heavy=3)
+    if rot:  # store every row ascending in (c - rot) mod m
+        for r in range(n):
+            a, b = int(rp[r]), int(rp[r + 1])
+            o = np.argsort((ci[a:b].astype(np.int64) - rot) % m, kind="stable")
+            ci[a:b], va[a:b] = ci[a:b][o], va[a:b][o]
+    B = rng.standard_normal((m, ld)).astype(np.float32)
+    C0 = rng.standard_normal((n, ld)).astype(np.float32)
+    bias = rng.standard_normal(F).astype(np.float32)
+    base = orc.spmm(rp, ci, va, B, C_in=C0[:, :F].copy(), alpha=0.5, beta=2.0, acc64=True, F=F)
+    want = np.where(base + bias > 0, base + bias, 0.01 * (base + bias))
+    absrow = orc.spmm(rp, ci, np.abs(va), np.abs(B), acc64=True, F=F).max(1) * 0.5 + 2 * np.abs(C0[:, :F]).max(1) + 2
+    rpt, cit, vat = to_dev(torch, rp, ci, va)
+    Bt, bt = torch.from_numpy(B).cuda(), torch.from_numpy(bias).cuda()
+    old_b = mg.lib().mggcn_tune(b"blocks", nblk)
+    old_w = mg.lib().mggcn_tune(b"window", 32)
+    try:
+        plan = mg.SpmmPlan(rp.astype(np.uint32), colidx_host=ci, cols=m, F_hint=F, col_rot=rot, col_span=m, split_nnz=256)
+        assert plan.blocks == nblk
+        Ct = torch.from_numpy(C0).cuda()
+        mg.spmm(rpt, cit, vat, Bt, Ct, cols=m, F=F, alpha=0.5, beta=2.0, epi=mg.make_epilogue(mg.EPI_LEAKY_RELU, 0.01, bias=bt),
+                plan=plan)
+        cfg = mg.lib().mggcn_last_spmm_config().decode()
+        assert f"{nblk} column block(s)" in cfg and "spmm_kernel<" in cfg, cfg
+        got = Ct.cpu().numpy()
+        check(got[:, :F], want, absrow)
+        assert np.array_equal(got[:, F:], C0[:, F:])  # padding columns untouched
+        # beta = 0 must not read C (NaN-poisoned) and must zero rows that are empty in every block
+        Cn = torch.full((n, ld), float("nan"), device="cuda")
+        mg.spmm(rpt, cit, vat, Bt, Cn, cols=m, F=F, plan=plan)
+        g0 = Cn.cpu().numpy()[:, :F]
+        assert np.isfinite(g0).all() and np.all(g0[1] == 0.0)
+        check(g0, orc.spmm(rp, ci, va, B, acc64=True, F=F), absrow)
+        # deterministic
+        Cn2 = torch.empty((n, ld), device="cuda")
+        mg.spmm(rpt, cit, vat, Bt, Cn2, cols=m, F=F, plan=plan)
+        assert torch.equal(Cn2[:, :F], Cn[:, :F])
+    finally:
+        mg.lib().mggcn_tune(b"blocks", old_b)
+        mg.lib().mggcn_tune(b"window", old_w)
+
+
+def test_blocked_plan_rejects_unsorted_rows_and_picks_one_block_when_b_fits(mg, cuda):
+    rp = np.array([0, 3, 5], np.uint32)
+    ci = np.array([4, 2, 7, 0, 1], np.uint32)  # row 0 is not ascending
+    old = mg.lib().mggcn_tune(b"blocks", 2)
+    try:
+        with pytest.raises(mg.MggcnError):
+            mg.SpmmPlan(rp, colidx_host=ci, cols=8, F_hint=32)
+    finally:
+        mg.lib().mggcn_tune(b"blocks", old)
+    ci = np.array([2, 4, 7, 0, 1], np.uint32)
+    plan = mg.SpmmPlan(rp, colidx_host=ci, cols=8, F_hint=128)  # automatic: a B of 4 KB needs no blocks
+    assert plan.blocks == 1
+
+
+def test_row_pointers_past_2_to_32(mg, orc, cuda):
+    """int64 row pointers with VALUES beyond 2^32 (papers100M-shape territory, north_star `matrix.hpp` item): the
+    i64 entry point addresses colidx / vals with 64-bit offsets.  The CSR arrays are allocated at their real size
+    (2^32 + 12345 + nnz entries: 17 GB each, a tenth of a B200) and the test's entries sit at the far end, so the
+    kernel and the plan see genuine row-pointer values beyond 2^32; the entries before them are never read."""
+    torch = cuda
+    rng = np.random.default_rng(9)
+    n, m, F = 900, 700, 128
+    rp, ci, va = random_csr(rng, n, m, 35, heavy=2)
+    nnz = len(ci)
+    off = (1 << 32) + 12345
+    big_ci = torch.empty(off + nnz, dtype=torch.int32, device="cuda")
+    big_va = torch.empty(off + nnz, dtype=torch.float32, device="cuda")
+    big_ci[off:] = torch.from_numpy(ci.view(np.int32)).cuda()
+    big_va[off:] = torch.from_numpy(va).cuda()
+    rp64 = (rp.astype(np.uint64) + np.uint64(off))
+    assert int(rp64[0]) > 2 ** 32
+    rpt = torch.from_numpy(rp64.astype(np.int64)).cuda()
+    B = rng.standard_normal((m, F)).astype(np.float32)
+    Bt = torch.from_numpy(B).cuda()
+    want = orc.spmm(rp, ci, va, B, acc64=True)
+    absrow = orc.spmm(rp, ci, np.abs(va), np.abs(B), acc64=True).max(1)
+    for plan in (None, mg.SpmmPlan(rp64)):
+        Ct = torch.empty((n, F), device="cuda")
+        mg.spmm(rpt, big_ci, big_va, Bt, Ct, cols=m, F=F, plan=plan)
+        check(Ct.cpu().numpy(), want, absrow)
+    del big_ci, big_va
+    torch.cuda.empty_cache()

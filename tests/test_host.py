@@ -176,3 +176,32 @@ def test_init_weights_match_reference_stream(mg, orc):
 
 def test_class_padding_rule(mg):
     assert [mg.pad_classes(41, P) for P in (1, 2, 4, 8)] == [41, 42, 44, 48]  # src/main.cpp:135
+
+
+@pytest.mark.parametrize("shape,scale,P", [("oracle4k", 1.0, 3), ("reddit", 0.01, 2), ("proteins", 0.02, 5),
+                                           ("papers100M", 0.00004, 8)])
+def test_sharded_generation_and_prep_bit_exact(mg, shape, scale, P):
+    """N4: a rank builds ONLY its row slab (mggcn_gen_rows_begin) and derives both aggregation operands from the
+    slab plus the vertex degrees; the P x P blocks must equal normalise -> transpose -> split of the whole graph
+    (src/main.cpp:139-151) bit for bit, also when N % P != 0."""
+    permute = shape != "papers100M"
+    A, X, Y, C = mg.generate(shape, seed=1, scale=scale, permute=permute)
+    N = A.n
+    cuts = mg.row_cuts(N, P)
+    deg = np.diff(A.rowptr.astype(np.int64)).astype(np.uint32)
+    A2 = A.copy()
+    A2.normalize(True)
+    AT = A2.transpose()
+    for r in range(P):
+        r0, r1 = int(cuts[r]), int(cuts[r + 1])
+        slab, Xl, Yl, _ = mg.generate_rows(shape, r0, r1, seed=1, scale=scale, permute=permute)
+        assert np.array_equal(slab.rowptr, A.rowptr[r0:r1 + 1] - A.rowptr[r0])
+        assert np.array_equal(slab.colidx, A.colidx[int(A.rowptr[r0]):int(A.rowptr[r1])])
+        assert np.array_equal(Xl, X[r0:r1]) and np.array_equal(Yl, Y[r0:r1])
+        fwd, bwd = mg.slab_operands(slab, deg, r0)
+        local = np.array([0, slab.n], np.uint32)
+        for mine, want in ((fwd.block_rows(local, cuts, only_row=0), AT.block_rows(cuts, cuts, only_row=r)),
+                           (bwd.block_rows(local, cuts, only_row=0), A2.block_rows(cuts, cuts, only_row=r))):
+            for a, b in zip(mine, want):
+                assert np.array_equal(a.rowptr, b.rowptr) and np.array_equal(a.colidx, b.colidx)
+                assert np.array_equal(a.vals.view(np.uint32), b.vals.view(np.uint32))
