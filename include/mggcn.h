@@ -297,6 +297,10 @@ MGGCN_API int mggcn_gen_labels(int64_t n_raw, int64_t n_padded, int num_classes,
 MGGCN_API int mggcn_gen_features_rows(int64_t n_raw, int64_t n_padded, int64_t f_raw,
                                       int64_t f_padded, uint64_t seed, int permute, int64_t row_begin,
                                       int64_t row_end, float *out);
+/* feature rows of `count` arbitrary vertex ids (out: count x f_padded) */
+MGGCN_API int mggcn_gen_features_ids(int64_t n_raw, int64_t n_padded, int64_t f_raw, int64_t f_padded,
+                                     uint64_t seed, int permute, const uint32_t *ids, int64_t count,
+                                     float *out);
 MGGCN_API int mggcn_gen_labels_rows(int64_t n_raw, int64_t n_padded, int num_classes, uint64_t seed,
                                     int permute, int64_t row_begin, int64_t row_end, int32_t *out);
 /* Weight init of the reference: std::default_random_engine(99) re-seeded per matrix,
@@ -390,9 +394,15 @@ MGGCN_API void *mggcn_engine_stream(mggcn_engine_t *e, int which);
 MGGCN_API int mggcn_engine_get(mggcn_engine_t *e, const char *name, float *out, size_t cap,
                                size_t *count);
 MGGCN_API int mggcn_engine_set(mggcn_engine_t *e, const char *name, const float *in, size_t count);
+/* rows [row_begin, row_end) of a named tensor (sampled checks at sizes where a whole activation is gigabytes) */
+MGGCN_API int mggcn_engine_get_rows(mggcn_engine_t *e, const char *name, int64_t row_begin, int64_t row_end,
+                                    float *out, size_t cap, size_t *count);
 /* Timers in the reference's CSV schema "<name>:<ms>\n" (src/matrix.hpp:149-157). */
 MGGCN_API int mggcn_engine_dump_timers(mggcn_engine_t *e, const char *prefix, char *buf,
                                        size_t cap, size_t *written);
+/* After an eager epoch with timers: one line "<timer name>\t<mggcn_last_spmm_config text>" per SpMM region, i.e.
+ * which kernel instance and schedule each aggregation really launched. */
+MGGCN_API int mggcn_engine_spmm_configs(mggcn_engine_t *e, char *buf, size_t cap, size_t *written);
 /* Switches between graph replay (the product path) and eager execution with named timers. */
 MGGCN_API int mggcn_engine_set_mode(mggcn_engine_t *e, int use_graph, int timers);
 MGGCN_API int64_t mggcn_engine_launches_per_epoch(mggcn_engine_t *e);

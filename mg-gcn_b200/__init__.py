@@ -105,6 +105,7 @@ _SIGS = {
     "mggcn_gen_rows_begin": (C.c_int, [_i64, _i64, _i32, C.c_double, _i64, C.c_uint64, _i32, _i64, _i64, C.POINTER(_vp),
                                        C.POINTER(_i64), C.POINTER(_i64)]),
     "mggcn_gen_features_rows": (C.c_int, [_i64, _i64, _i64, _i64, C.c_uint64, _i32, _i64, _i64, _vp]),
+    "mggcn_gen_features_ids": (C.c_int, [_i64, _i64, _i64, _i64, C.c_uint64, _i32, _vp, _i64, _vp]),
     "mggcn_gen_labels_rows": (C.c_int, [_i64, _i64, _i32, C.c_uint64, _i32, _i64, _i64, _vp]),
     "mggcn_gen_features": (C.c_int, [_i64, _i64, _i64, _i64, C.c_uint64, _i32, _vp]),
     "mggcn_gen_labels": (C.c_int, [_i64, _i64, _i32, C.c_uint64, _i32, _vp]),
@@ -125,6 +126,8 @@ _SIGS = {
     "mggcn_engine_stream": (_vp, [_vp, _i32]),
     "mggcn_engine_get": (C.c_int, [_vp, C.c_char_p, _vp, _sz, C.POINTER(_sz)]),
     "mggcn_engine_set": (C.c_int, [_vp, C.c_char_p, _vp, _sz]),
+    "mggcn_engine_get_rows": (C.c_int, [_vp, C.c_char_p, _i64, _i64, _vp, _sz, C.POINTER(_sz)]),
+    "mggcn_engine_spmm_configs": (C.c_int, [_vp, _vp, _sz, C.POINTER(_sz)]),
     "mggcn_engine_dump_timers": (C.c_int, [_vp, C.c_char_p, _vp, _sz, C.POINTER(_sz)]),
     "mggcn_engine_set_mode": (C.c_int, [_vp, _i32, _i32]),
     "mggcn_engine_launches_per_epoch": (_i64, [_vp]),
@@ -278,8 +281,15 @@ SHAPES = {
     "reddit": (232965, 114615892, 602, 41, 1, 2.6, 21657),
     "products": (2449029, 123718280, 100, 47, 1, 2.9, 17481),
     "proteins": (132534, 79122504, 8, 112, 0, 0.0, 0),
-    "papers100M": (111059956, 3231371744, 128, 172, 1, 2.8, 100000),
+    # uniform-random neighbours and no vertex permutation: every rank walks the whole sample stream (1.6 B pairs) to
+    # build its slab, and the power-law sampler's random table look-ups per endpoint would make that minutes per rank
+    "papers100M": (111059956, 3231371744, 128, 172, 0, 0.0, 0),
 }
+# shapes whose generator output needs no balancing permutation (uniform degrees)
+UNPERMUTED = {"papers100M"}
+# hidden layers of BASELINE.json's configs
+HIDDEN = {"oracle4k": [64], "reddit": [128, 128, 128], "products": [256, 256, 256], "proteins": [128, 128, 128],
+          "papers100M": [128, 128, 128]}
 
 
 def generate(shape, seed=1, permute=True, scale=1.0, features=True):
@@ -339,6 +349,17 @@ def generate_rows(shape, r0, r1, seed=1, permute=True, scale=1.0, features=True)
         Y = np.empty(r1 - r0, dtype=np.int32)
         check(lib().mggcn_gen_labels_rows(n_raw, n.value, classes, seed, int(permute), r0, r1, Y.ctypes.data))
     return slab, X, Y, classes
+
+
+def generate_feature_rows(shape, ids, seed=1, permute=True, scale=1.0):
+    """Feature rows of arbitrary vertex ids of generate(shape, ...)."""
+    n_raw, edges, f_raw, classes, model, gamma, max_deg = shape_params(shape, scale)
+    n = (n_raw + 7) // 8 * 8
+    f8 = (f_raw + 7) // 8 * 8
+    ids = np.ascontiguousarray(ids, dtype=np.uint32)
+    out = np.empty((len(ids), f8), dtype=np.float32)
+    check(lib().mggcn_gen_features_ids(n_raw, n, f_raw, f8, seed, int(permute), ids.ctypes.data, len(ids), out.ctypes.data))
+    return out
 
 
 def write_dataset(dirname, A, X, Y, ordinal_bytes=4):
@@ -582,6 +603,21 @@ class Engine:
         check(lib().mggcn_engine_get(self.handle, name.encode(), out.ctypes.data, n.value, C.byref(n)))
         return out
 
+    def get_rows(self, name, r0, r1):
+        n = C.c_size_t()
+        check(lib().mggcn_engine_get_rows(self.handle, name.encode(), r0, r1, None, 0, C.byref(n)))
+        out = np.empty(n.value, dtype=np.float32)
+        check(lib().mggcn_engine_get_rows(self.handle, name.encode(), r0, r1, out.ctypes.data, n.value, C.byref(n)))
+        return out.reshape(r1 - r0, -1)
+
+    def spmm_configs(self):
+        """{timer name: kernel instance + schedule} of the SpMM regions of the last eager epoch with timers."""
+        n = C.c_size_t()
+        check(lib().mggcn_engine_spmm_configs(self.handle, None, 0, C.byref(n)))
+        buf = (C.c_char * (n.value + 1))()
+        check(lib().mggcn_engine_spmm_configs(self.handle, buf, n.value + 1, C.byref(n)))
+        return dict(l.split("\t", 1) for l in bytes(buf).rstrip(b"\0").decode().splitlines() if "\t" in l)
+
     def set(self, name, value):
         v = np.ascontiguousarray(value, dtype=np.float32).ravel()
         check(lib().mggcn_engine_set(self.handle, name.encode(), v.ctypes.data, v.size))
@@ -609,12 +645,12 @@ class Engine:
         self.close()
 
 
-def build_rank_engine(A, sizes, world=1, rank=0, device=0, **kw):
+def build_rank_engine(A, sizes, world=1, rank=0, device=0, cuts=None, **kw):
     """Host pre-processing of src/main.cpp:139-151 for one rank: normalise by column, transpose,
     P x P split, then an Engine holding this rank's block rows of A_T (forward) and A (backward).
     A is consumed (normalised in place), like the reference's csr_matrix::normalize."""
     N = A.n
-    cuts = row_cuts(N, world)
+    cuts = row_cuts(N, world) if cuts is None else np.ascontiguousarray(cuts, dtype=np.uint32)
     A.normalize(by_column=True)
     A_T = A.transpose()
     eng = Engine(sizes, N, world=world, rank=rank, device=device, cuts=cuts, **kw)

@@ -272,6 +272,7 @@ struct layer_t {
 struct named_timer {
     std::string name;
     cudaEvent_t beg, end;
+    std::string cfg;  // SpMM regions: the kernel instance and schedule that ran inside (mggcn_last_spmm_config)
 };
 
 }  // namespace
@@ -378,9 +379,10 @@ int timer_begin(eng *e, const std::string &name, cudaStream_t st, int *slot) {
     MGGCN_CUDA_TRY(cudaEventRecord(e->timers[*slot].beg, st));
     return MGGCN_OK;
 }
-int timer_end(eng *e, cudaStream_t st, int slot) {
+int timer_end(eng *e, cudaStream_t st, int slot, bool spmm = false) {
     if (slot < 0) return MGGCN_OK;
     MGGCN_CUDA_TRY(cudaEventRecord(e->timers[slot].end, st));
+    if (spmm) e->timers[slot].cfg = mggcn_last_spmm_config();
     return MGGCN_OK;
 }
 
@@ -417,7 +419,7 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
         TRY(timer_begin(e, tname + "matmul-spmm", e->sc, &ts));
         TRY(mggcn_spmm_csr_f32_i32(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, B, ld, C, ld, (int)F, 1.f, 0.f,
                                    epi, a.plan, e->ws_spmm));
-        TRY(timer_end(e, e->sc, ts));
+        TRY(timer_end(e, e->sc, ts, true));
         return MGGCN_OK;
     }
     const size_t off = (size_t)(reinterpret_cast<const char *>(B) - e->arena);
@@ -465,7 +467,7 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
                                                     e->ws_spmm);
             spmm_touched_cols_hint(-1);
             TRY(rc_g);
-            TRY(timer_end(e, e->sc, t_s));
+            TRY(timer_end(e, e->sc, t_s, true));
         }
         TRY(timer_end(e, e->sc, t_all));
         // nobody may overwrite B before every peer has pulled it
@@ -587,7 +589,7 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
         TRY(timer_begin(e, tname + std::to_string(s) + "_matmul-spmm-stage", e->sc, &t_s));
         TRY(mggcn_spmm_csr_f32_i32(e->sc, a.rows, a.cols, a.rowptr, a.colidx, a.vals, src, ld, C, ld, (int)F, 1.f,
                                    s == 0 ? 0.f : 1.f, last ? epi : nullptr, a.plan, e->ws_spmm));
-        TRY(timer_end(e, e->sc, t_s));
+        TRY(timer_end(e, e->sc, t_s, true));
         TRACE(e->rank, "dist_spmm: stage spmm launched");
         if (e->sm != e->sc) MGGCN_CUDA_TRY(cudaEventRecord(e->ev_spmm[s], e->sc));
     }
@@ -1121,6 +1123,17 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
     return MGGCN_OK;
 }
 
+// host rows (pitch = width floats) into device rows of pitch ld: one flat copy when the pitches agree
+static int copy_rows_in(float *dst, int64_t ld, const float *src, int64_t width, int64_t rows, cudaStream_t st) {
+    if (ld == width) {
+        MGGCN_CUDA_TRY(cudaMemcpyAsync(dst, src, (size_t)rows * (size_t)width * 4, cudaMemcpyDefault, st));
+    } else {
+        MGGCN_CUDA_TRY(cudaMemcpy2DAsync(dst, (size_t)ld * 4, src, (size_t)width * 4, (size_t)width * 4, (size_t)rows,
+                                         cudaMemcpyDefault, st));
+    }
+    return MGGCN_OK;
+}
+
 int mggcn_engine_set_inputs(mggcn_engine_t *e, const float *X_host, const int32_t *Y_host, int async) {
     if (!e) return fail(MGGCN_E_INVALID, "null engine");
     TRY(set_dev(e));
@@ -1135,9 +1148,7 @@ int mggcn_engine_set_inputs(mggcn_engine_t *e, const float *X_host, const int32_
             MGGCN_CUDA_TRY(cudaEventCreateWithFlags(&e->ev_swap, cudaEventDisableTiming));
         }
         if (e->swap_recorded) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->scopy, e->ev_swap, 0));  // WAR on the shadows
-        if (X_host)
-            MGGCN_CUDA_TRY(cudaMemcpy2DAsync(e->X_shadow, (size_t)e->ldX * 4, X_host, (size_t)e->sizes[0] * 4,
-                                             (size_t)e->sizes[0] * 4, (size_t)e->n, cudaMemcpyDefault, e->scopy));
+        if (X_host) TRY(copy_rows_in(e->X_shadow, e->ldX, X_host, e->sizes[0], e->n, e->scopy));
         if (Y_host) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y_shadow, Y_host, (size_t)e->n * 4, cudaMemcpyDefault, e->scopy));
         MGGCN_CUDA_TRY(cudaEventRecord(e->ev_pref, e->scopy));
         e->pref_x = e->pref_x || X_host;
@@ -1146,9 +1157,7 @@ int mggcn_engine_set_inputs(mggcn_engine_t *e, const float *X_host, const int32_
     }
     // ordered after everything already queued on the compute stream (the previous epoch reads X)
     cudaStream_t st = e->sc;
-    if (X_host)
-        MGGCN_CUDA_TRY(cudaMemcpy2DAsync(e->X, (size_t)e->ldX * 4, X_host, (size_t)e->sizes[0] * 4, (size_t)e->sizes[0] * 4,
-                                         (size_t)e->n, cudaMemcpyDefault, st));
+    if (X_host) TRY(copy_rows_in(e->X, e->ldX, X_host, e->sizes[0], e->n, st));
     if (Y_host) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y, Y_host, (size_t)e->n * 4, cudaMemcpyDefault, st));
     if (!async) MGGCN_CUDA_TRY(cudaStreamSynchronize(st));
     return MGGCN_OK;
@@ -1403,6 +1412,37 @@ int mggcn_engine_dump_timers(mggcn_engine_t *e, const char *prefix, char *buf, s
         memcpy(buf, s.data(), k);
         buf[k] = 0;
     }
+    return MGGCN_OK;
+}
+
+int mggcn_engine_spmm_configs(mggcn_engine_t *e, char *buf, size_t cap, size_t *written) {
+    if (!e || !written) return fail(MGGCN_E_INVALID, "bad argument");
+    std::string s;
+    for (const named_timer &t : e->timers)
+        if (!t.cfg.empty()) s += t.name + "\t" + t.cfg + "\n";
+    *written = s.size();
+    if (buf && cap) {
+        const size_t k = std::min(cap - 1, s.size());
+        memcpy(buf, s.data(), k);
+        buf[k] = 0;
+    }
+    return MGGCN_OK;
+}
+
+int mggcn_engine_get_rows(mggcn_engine_t *e, const char *name, int64_t row_begin, int64_t row_end, float *out, size_t cap,
+                          size_t *count) {
+    if (!e || !count) return fail(MGGCN_E_INVALID, "bad argument");
+    TRY(set_dev(e));
+    float *p; int64_t r, c, ld;
+    TRY(find_tensor(e, name, &p, &r, &c, &ld));
+    if (row_begin < 0 || row_begin > row_end || row_end > r) return fail(MGGCN_E_INVALID, "rows [%lld, %lld) outside %s", (long long)row_begin, (long long)row_end, name);
+    *count = (size_t)((row_end - row_begin) * c);
+    if (!out) return MGGCN_OK;
+    if (cap < *count) return fail(MGGCN_E_INVALID, "buffer too small for %s", name);
+    TRY(mggcn_engine_sync(e));
+    if (*count)
+        MGGCN_CUDA_TRY(cudaMemcpy2D(out, (size_t)c * 4, p + row_begin * ld, (size_t)ld * 4, (size_t)c * 4, (size_t)(row_end - row_begin),
+                                    cudaMemcpyDefault));
     return MGGCN_OK;
 }
 

@@ -36,14 +36,14 @@ std::vector<uint32_t> make_perm(int64_t n, uint64_t seed) {
     return perm;
 }
 
-// Vose alias table over n weights
+// Vose alias table over n weights; probability and alias of a slot share one 8-byte entry, so a sample costs one
+// cache miss (the table of a 111 M-vertex graph is 0.9 GB and every sample is a random access)
 struct alias_table {
-    std::vector<float> prob;
-    std::vector<uint32_t> alias;
+    struct slot_t { float prob; uint32_t alias; };
+    std::vector<slot_t> slots;
     void build(const std::vector<double> &w) {
         const size_t n = w.size();
-        prob.assign(n, 0.f);
-        alias.assign(n, 0);
+        slots.assign(n, slot_t{0.f, 0});
         double total = 0;
         for (double x : w) total += x;
         std::vector<double> scaled(n);
@@ -57,19 +57,20 @@ struct alias_table {
         while (!small.empty() && !large.empty()) {
             uint32_t s = small.back(), l = large.back();
             small.pop_back();
-            prob[s] = (float)scaled[s];
-            alias[s] = l;
+            slots[s].prob = (float)scaled[s];
+            slots[s].alias = l;
             scaled[l] = (scaled[l] + scaled[s]) - 1.0;
             if (scaled[l] < 1.0) { large.pop_back(); small.push_back(l); }
         }
-        for (uint32_t i : large) { prob[i] = 1.f; alias[i] = i; }
-        for (uint32_t i : small) { prob[i] = 1.f; alias[i] = i; }
+        for (uint32_t i : large) { slots[i].prob = 1.f; slots[i].alias = i; }
+        for (uint32_t i : small) { slots[i].prob = 1.f; slots[i].alias = i; }
     }
     inline uint32_t sample(uint64_t h) const {
-        const size_t n = prob.size();
+        const size_t n = slots.size();
         uint64_t slot = (h >> 32) * (uint64_t)n >> 32;           // top 32 bits pick the slot
         float u = (float)(h & 0xFFFFFFull) * (1.0f / 16777216.0f);  // low 24 bits pick the side
-        return u < prob[slot] ? (uint32_t)slot : alias[slot];
+        const slot_t s = slots[slot];
+        return u < s.prob ? (uint32_t)slot : s.alias;
     }
 };
 
@@ -97,17 +98,26 @@ static int gen_rows(int64_t n_raw, int64_t target_directed_edges, int degree_mod
         // vertex has expected degree max_deg.
         const double a = 1.0 / std::max(1e-3, gamma - 1.0);
         auto top_degree = [&](double i0) {
-            // fixed 64Ki blocks summed in block order: the same value for any thread count
-            const int64_t nb = (n_raw + 65535) / 65536;
+            // fixed 64Ki blocks summed in block order: the same value for any thread count.  Past 4 Mi vertices
+            // (papers100M-shape: 60 bisection steps x 111 M pow() calls would take minutes) only the first 4 Mi
+            // terms are summed and the smooth tail is integrated (midpoint rule, relative error < 1e-9 there);
+            // graphs below that size are generated exactly as before.
+            const int64_t n_sum = std::min<int64_t>(n_raw, 4ll << 20);
+            double tail = 0;
+            if (n_sum < n_raw) {
+                const double x0 = (double)n_sum - 0.5 + i0, x1 = (double)n_raw - 0.5 + i0;
+                tail = std::fabs(a - 1.0) < 1e-12 ? std::log(x1 / x0) : (std::pow(x1, 1.0 - a) - std::pow(x0, 1.0 - a)) / (1.0 - a);
+            }
+            const int64_t nb = (n_sum + 65535) / 65536;
             std::vector<double> part((size_t)nb);
 #pragma omp parallel for schedule(static)
             for (int64_t b = 0; b < nb; ++b) {
                 double s = 0;
-                const int64_t hi_i = std::min<int64_t>(n_raw, (b + 1) * 65536);
+                const int64_t hi_i = std::min<int64_t>(n_sum, (b + 1) * 65536);
                 for (int64_t i = b * 65536; i < hi_i; ++i) s += std::pow((double)i + i0, -a);
                 part[b] = s;
             }
-            double W = 0;
+            double W = tail;
             for (double s : part) W += s;
             return 2.0 * (double)E * std::pow(i0, -a) / W;
         };
@@ -143,31 +153,54 @@ static int gen_rows(int64_t n_raw, int64_t target_directed_edges, int degree_mod
         }
     };
 
-    // pass 1: degrees (both directions); self pairs are dropped, the self-loop is added later
+    const bool trace = getenv("MGGCN_GEN_TRACE") != nullptr;
+    double t_prev = omp_get_wtime();
+    auto lap = [&](const char *what) {
+        if (!trace) return;
+        const double t = omp_get_wtime();
+        fprintf(stderr, "[gen] %-28s %.3f s\n", what, t - t_prev);
+        t_prev = t;
+    };
+    lap("tables");
+    // pass 1: one walk over the sample stream; the (local row, column) pairs that touch these rows go into
+    // per-thread buffers and are counted.  Self pairs are dropped, the self-loop is added later.
     std::vector<std::atomic<uint32_t>> deg((size_t)nl);
     for (auto &d : deg) d.store(0, std::memory_order_relaxed);
-#pragma omp parallel for schedule(static)
-    for (int64_t k = 0; k < E; ++k) {
-        uint32_t u, v;
-        endpoints(k, u, v);
-        if (u == v) continue;
-        if (mine(u)) deg[u - lo32].fetch_add(1, std::memory_order_relaxed);
-        if (mine(v)) deg[v - lo32].fetch_add(1, std::memory_order_relaxed);
+    const int T = std::max(1, omp_get_max_threads());
+    std::vector<std::vector<uint64_t>> kept((size_t)T);
+#pragma omp parallel num_threads(T)
+    {
+        std::vector<uint64_t> &mine_buf = kept[(size_t)omp_get_thread_num()];
+        mine_buf.reserve((size_t)((double)E * 2.2 * (double)nl / (double)n / T) + 1024);
+#pragma omp for schedule(static)
+        for (int64_t k = 0; k < E; ++k) {
+            uint32_t u, v;
+            endpoints(k, u, v);
+            if (u == v) continue;
+            if (mine(u)) {
+                deg[u - lo32].fetch_add(1, std::memory_order_relaxed);
+                mine_buf.push_back((uint64_t)(u - lo32) << 32 | v);
+            }
+            if (mine(v)) {
+                deg[v - lo32].fetch_add(1, std::memory_order_relaxed);
+                mine_buf.push_back((uint64_t)(v - lo32) << 32 | u);
+            }
+        }
     }
+    lap("sample + keep");
     std::vector<uint64_t> start((size_t)nl + 1, 0);
     for (int64_t i = 0; i < nl; ++i) start[i + 1] = start[i] + deg[i].load(std::memory_order_relaxed);
     std::vector<uint32_t> raw(start[nl]);
     std::vector<std::atomic<uint64_t>> cursor((size_t)nl);
     for (int64_t i = 0; i < nl; ++i) cursor[i].store(start[i], std::memory_order_relaxed);
-    // pass 2: scatter (order inside a row is arbitrary here, fixed by the sort below)
-#pragma omp parallel for schedule(static)
-    for (int64_t k = 0; k < E; ++k) {
-        uint32_t u, v;
-        endpoints(k, u, v);
-        if (u == v) continue;
-        if (mine(u)) raw[cursor[u - lo32].fetch_add(1, std::memory_order_relaxed)] = v;
-        if (mine(v)) raw[cursor[v - lo32].fetch_add(1, std::memory_order_relaxed)] = u;
+    // pass 2: scatter from the buffers (order inside a row is arbitrary here, fixed by the sort below)
+#pragma omp parallel num_threads(T)
+    {
+        std::vector<uint64_t> &mine_buf = kept[(size_t)omp_get_thread_num()];
+        for (uint64_t pr : mine_buf) raw[cursor[pr >> 32].fetch_add(1, std::memory_order_relaxed)] = (uint32_t)pr;
+        std::vector<uint64_t>().swap(mine_buf);
     }
+    lap("scatter");
     // pass 3: sort + dedup each row, insert the self-loop
     std::vector<uint32_t> final_deg((size_t)nl);
 #pragma omp parallel for schedule(dynamic, 256)
@@ -194,6 +227,7 @@ static int gen_rows(int64_t n_raw, int64_t target_directed_edges, int degree_mod
         *o++ = self;
         while (k < cnt) { *o++ = b[k]; ++k; }
     }
+    lap("sort + dedup + self-loops");
     *out = g;
     *n_padded = n;
     *nnz = (int64_t)g->rowptr[nl];
@@ -271,6 +305,30 @@ int mggcn_gen_features_rows(int64_t n_raw, int64_t n_padded, int64_t f_raw, int6
             else
                 row[j] = 0.f;
         }
+    }
+    return MGGCN_OK;
+}
+
+// Feature rows of an arbitrary list of (permuted) vertex ids -- sampled checks need the rows of a vertex's
+// neighbours, wherever they live.
+int mggcn_gen_features_ids(int64_t n_raw, int64_t n_padded, int64_t f_raw, int64_t f_padded, uint64_t seed, int permute,
+                           const uint32_t *ids, int64_t count, float *out) {
+    if (!out || !ids || n_raw > n_padded || f_raw > f_padded || count < 0) return fail(MGGCN_E_INVALID, "bad argument");
+    std::vector<uint32_t> inv;
+    if (permute) {
+        const std::vector<uint32_t> perm = make_perm(n_padded, seed ? seed : 1);
+        inv.resize((size_t)n_padded);
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n_padded; ++i) inv[perm[i]] = (uint32_t)i;
+    }
+    for (int64_t k = 0; k < count; ++k)
+        if ((int64_t)ids[k] >= n_padded) return fail(MGGCN_E_INVALID, "vertex id out of range");
+#pragma omp parallel for schedule(static)
+    for (int64_t k = 0; k < count; ++k) {
+        const int64_t i = permute ? (int64_t)inv[ids[k]] : (int64_t)ids[k];
+        float *row = out + (size_t)k * f_padded;
+        for (int64_t j = 0; j < f_padded; ++j)
+            row[j] = i < n_raw && j < f_raw ? (float)(2.0 * u01(hash2(seed ^ 0x46454154ull, (uint64_t)i * f_raw + j)) - 1.0) : 0.f;
     }
     return MGGCN_OK;
 }

@@ -22,6 +22,9 @@ def main():
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--epochs", type=int, default=10)
     ap.add_argument("--hidden", type=int, nargs="+", default=[64, 64])
+    ap.add_argument("--skew", type=int, default=0, help="move every inner cut by this many rows: uneven row blocks "
+                                                        "(the reference's dense side needs N % P == 0, SURVEY D7; the engine does not)")
+    ap.add_argument("--sharded", action="store_true", help="bench.py's pre-processing: every rank builds only its slab")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -43,14 +46,28 @@ def main():
             idt.copy_(torch.frombuffer(bytearray(bytes(buf)), dtype=torch.uint8))
         dist.broadcast(idt, 0)
         nccl_id = bytes(idt.cpu().numpy().tobytes())
-    eng, A_T = mg.build_rank_engine(A, sizes, world=world, rank=rank, device=local, use_graph=args.graph,
-                                    nccl_id=nccl_id, comm=comm, overlap=not args.no_overlap)
+    cuts = mg.row_cuts(N, world)
+    for i in range(1, world):
+        cuts[i] += args.skew * (1 if i % 2 else -1)
+    if args.sharded:
+        r0, r1 = int(cuts[rank]), int(cuts[rank + 1])
+        slab, _, _, _ = mg.generate_rows("oracle4k", r0, r1, seed=1)
+        dl = torch.from_numpy(np.diff(slab.rowptr.astype(np.int64)).astype(np.int32)).cuda()
+        parts = [torch.empty(int(cuts[r + 1] - cuts[r]), dtype=torch.int32, device="cuda") for r in range(world)]
+        dist.all_gather(parts, dl)
+        deg_all = torch.cat(parts).cpu().numpy().astype(np.uint32)
+        eng, _, _ = mg.build_rank_engine_sharded(slab, deg_all, sizes, world=world, rank=rank, device=local, cuts=cuts,
+                                                 use_graph=args.graph, nccl_id=nccl_id, comm=comm, overlap=not args.no_overlap)
+        A.normalize(by_column=True)
+        A_T = A.transpose()
+    else:
+        eng, A_T = mg.build_rank_engine(A, sizes, world=world, rank=rank, device=local, cuts=cuts, use_graph=args.graph,
+                                        nccl_id=nccl_id, comm=comm, overlap=not args.no_overlap)
     if comm != mg.COMM_NCCL:
         ht = torch.frombuffer(bytearray(eng.comm_handle()), dtype=torch.uint8).cuda()
         allh = [torch.empty_like(ht) for _ in range(world)]
         dist.all_gather(allh, ht)
         eng.comm_connect([bytes(t.cpu().numpy().tobytes()) for t in allh])
-    cuts = mg.row_cuts(N, world)
     r0, r1 = int(cuts[rank]), int(cuts[rank + 1])
     eng.set_inputs(np.ascontiguousarray(X[r0:r1]), np.ascontiguousarray(Y[r0:r1]))
     ref = orc.Gcn(sizes, N, (A_T.rowptr, A_T.colidx, A_T.vals), (A.rowptr, A.colidx, A.vals), P=world, cuts=cuts)
@@ -114,7 +131,8 @@ def main():
     eng.close()
     dist.barrier()
     if rank == 0:
-        print(f"dist check ok: world={world} comm={args.comm} graph={args.graph} worst layer rel err {worst:.2e}", flush=True)
+        print(f"dist check ok: world={world} comm={args.comm} graph={args.graph} overlap={not args.no_overlap} skew={args.skew} "
+              f"sharded={args.sharded} worst layer rel err {worst:.2e}", flush=True)
     dist.destroy_process_group()
 
 

@@ -149,23 +149,45 @@ def test_state_errors(mg, cuda):
     eng.close()
 
 
+def run_dist_check(cuda, world, port, *extra):
+    import os
+    import subprocess
+    import sys
+    if cuda.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs (gpurun --gpus {world})")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.join(root, "tests", "dist_engine_check.py"), *extra]
+    env = dict(os.environ, MGGCN_BARRIER_TIMEOUT_MS="5000")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert "dist check ok" in r.stdout
+    return r.stdout
+
+
 @pytest.mark.parametrize("comm,graph", [("nccl", False), ("p2p", False), ("p2p", True), ("nccl", True),
                                         ("p2p-staged", False), ("p2p-staged", True), ("p2p-grouped", False), ("p2p-grouped", True)])
 def test_two_gpu_engine_matches_oracle(cuda, comm, graph):
     """One process per GPU (torchrun), world 2: staged exchange + SpMM, gradient reduction, Adam."""
-    import os
-    import subprocess
-    import sys
-    if cuda.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-           "127.0.0.1", "--master-port", "29611", os.path.join(root, "tests", "dist_engine_check.py"), "--comm", comm]
-    if graph:
-        cmd.append("--graph")
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
-    assert "dist check ok" in r.stdout
+    run_dist_check(cuda, 2, 29611, "--comm", comm, *(["--graph"] if graph else []))
+
+
+@pytest.mark.parametrize("comm", ["nccl", "p2p-staged", "p2p-grouped"])
+def test_two_gpu_no_overlap_matches_oracle(cuda, comm):
+    """Row a4 (src/cuda_utils.hpp:47-55, the CLI's -S): the exchange runs on the compute stream."""
+    run_dist_check(cuda, 2, 29612, "--comm", comm, "--no-overlap")
+
+
+@pytest.mark.parametrize("comm,graph", [("p2p-staged", False), ("p2p-grouped", True), ("p2p", True), ("nccl", False)])
+def test_two_gpu_uneven_row_blocks(cuda, comm, graph):
+    """Row blocks of different sizes (N % P != 0 in general): peers address each other's buffers at this rank's own
+    arena offsets, so the arena layout must not depend on the local row count."""
+    run_dist_check(cuda, 2, 29613, "--comm", comm, "--skew", "37", *(["--graph"] if graph else []))
+
+
+def test_two_gpu_sharded_preprocessing(cuda):
+    """bench.py's path: every rank generates its own slab and derives both operands from it."""
+    run_dist_check(cuda, 2, 29615, "--comm", "p2p-grouped", "--graph", "--sharded")
 
 
 @pytest.mark.parametrize("graph", [False, True])
@@ -173,16 +195,30 @@ def test_four_gpu_grouped_exchange_matches_oracle(cuda, graph):
     """World 4: the grouped exchange multiplies stages 2-3 in one launch over the all-gather buffer (a group with
     more than one block only exists from 4 ranks on).  Same checker as the 2-GPU test: per-layer outputs, weight
     gradients and 10 epochs of loss against the oracle."""
+    run_dist_check(cuda, 4, 29614, "--comm", "p2p-grouped", *(["--graph"] if graph else []))
+
+
+@pytest.mark.parametrize("comm,extra", [("p2p-grouped", []), ("p2p-grouped", ["--graph"]), ("p2p-staged", ["--graph"]),
+                                        ("p2p-grouped", ["--no-overlap"]), ("p2p-grouped", ["--skew", "11"]),
+                                        ("nccl", []), ("p2p", ["--graph"])])
+def test_eight_gpu_engine_matches_oracle(cuda, comm, extra):
+    """World 8 -- the headline configuration.  Only here does the grouped exchange multiply stages 4-7 in ONE launch
+    over the all-gather buffer; the stage order (rank+s)%P differs from the reference's i = 0..P-1
+    (src/cuda_utils.hpp:82-83) on every rank.  Per-layer outputs, weight gradients, 10 epochs of loss against the
+    oracle's dist_gcn at P = 8, and bit-identical replicated weights across ranks."""
+    run_dist_check(cuda, 8, 29618, "--comm", comm, *extra)
+
+
+def test_two_gpu_bcast_stage(cuda):
+    """Row a5: mggcn_bcast_stage_f32 on its own NCCL communicator, every root in turn, uneven blocks."""
     import os
     import subprocess
     import sys
-    if cuda.cuda.device_count() < 4:
-        pytest.skip("needs 4 GPUs (gpurun --gpus 4)")
+    if cuda.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "4", "--master-addr",
-           "127.0.0.1", "--master-port", "29614", os.path.join(root, "tests", "dist_engine_check.py"), "--comm", "p2p-grouped"]
-    if graph:
-        cmd.append("--graph")
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29619", os.path.join(root, "tests", "dist_bcast_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
-    assert "dist check ok" in r.stdout
+    assert "bcast check ok" in r.stdout
