@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <limits>
 #include <omp.h>
 #include <random>
 #include <vector>
@@ -366,10 +367,15 @@ int mggcn_init_weights(int64_t rows, int64_t cols, float gain, float *out) {
     if (!out || rows <= 0 || cols <= 0) return fail(MGGCN_E_INVALID, "bad argument");
     // same engine, seed and distribution types as dn_matrix::init (src/matrix.hpp:539-545) so the
     // libstdc++ stream is reproduced draw for draw
+    // libstdc++'s uniform_real_distribution returns  canonical * (b - a) + a.  g++ contracts that into one fused
+    // multiply-add whenever the target has FMA (the reference builds with -O3 -march=native, and oracle/_ref with
+    // -march=x86-64-v3), so the reference binary's initial weights are the FMA results; written out here so the
+    // stream is bit-identical to the reference build whatever flags THIS file is compiled with.
     std::default_random_engine gen(99);
     gain *= std::sqrt(3.0 / rows);
-    std::uniform_real_distribution<float> uni(-gain, gain);
-    for (int64_t i = 0; i < rows * cols; ++i) out[i] = uni(gen);
+    const float a = -gain, b = gain;
+    for (int64_t i = 0; i < rows * cols; ++i)
+        out[i] = std::fmaf(std::generate_canonical<float, std::numeric_limits<float>::digits>(gen), b - a, a);
     return MGGCN_OK;
 }
 

@@ -22,6 +22,7 @@
 //   * B is the operand with reuse (each row is gathered avg-degree times): it is loaded with an
 //     L2 evict_last policy, the CSR stream with evict_first / no L1 allocation.
 #include <algorithm>
+#include <atomic>
 #include <numeric>
 #include <vector>
 
@@ -52,6 +53,7 @@ struct split_row {
 // split list are finished by the fix-up kernel.
 struct plan_block {
     int64_t first_item = 0, n_items = 0, n_seg = 0, first_split = 0, n_split = 0;
+    int64_t nnz = 0;  // entries covered by the items (the launch is made persistent when the items are short)
 };
 
 struct mggcn_spmm_plan {
@@ -76,6 +78,9 @@ int g_policy = 1;     // 1: L2 evict_last for B, evict_first for the CSR stream;
 int g_split = 0;      // row-split threshold of new plans; 0 = chosen from the matrix (see plan_create)
 int g_slices = 0;     // k > 1: run as k launches over F/k-wide column windows of B and C; 0: k = 2 when B (cols x F floats)
                       // is larger than half of the L2 but its half is not (see spmm_scheduled); 1: never
+int g_persist = 0;    // 0: persistent grid + next-item prefetch for launches of short items (avg < 96 entries); 1: always; 2: never
+int g_persist_waves = 1;  // persistent grid = this many times the resident CTA count
+int g_tma = 0;        // 1: F = 64 / 128 products gather B through the TMA unit (spmm_tma_kernel, experiment)
 int g_blocks = 0;     // column blocks of new blocked plans: 0 = from the traffic model, 1 = never, k = exactly k
 int g_window = 0;     // feature-window width of blocked plans at launch: 0 = widest that keeps a block's B rows resident
 int g_tile_mb = 0;    // bytes of B a launch may count on staying L2-resident, in MiB; 0 = 45 % of the L2
@@ -214,6 +219,33 @@ __device__ __forceinline__ float apply_epilogue(float x, const mggcn_epilogue &e
 // One group of LANES threads per item; NCH vectors of VEC floats per lane; the group covers
 // LANES*NCH*VEC features per pass and loops over passes when F is wider.
 // EXACT: F is a multiple of the pass width, so no per-lane column predicate is needed.
+// Header of a work item as the kernel uses it.
+struct item_hdr {
+    uint64_t begin;
+    uint32_t len, row;
+};
+__device__ __forceinline__ item_hdr load_hdr(const spmm_args &a, int64_t idx) {
+    item_hdr h{0, 0, 0};
+    if (idx < a.n_items) {
+        if (a.items) {
+            const spmm_item it = a.items[idx];
+            h.begin = it.begin; h.len = it.len; h.row = it.row;
+        } else {
+            h.row = (uint32_t)idx;
+            if (a.rowptr64) {
+                const uint64_t *rp = static_cast<const uint64_t *>(a.rowptr);
+                h.begin = rp[idx];
+                h.len = (uint32_t)(rp[idx + 1] - h.begin);
+            } else {
+                const uint32_t *rp = static_cast<const uint32_t *>(a.rowptr);
+                h.begin = rp[idx];
+                h.len = rp[idx + 1] - (uint32_t)h.begin;
+            }
+        }
+    }
+    return h;
+}
+
 template <int LANES, int NCH, int VEC, int UNROLL, bool EXACT, bool GATHER>
 __device__ __forceinline__ void spmm_body(const spmm_args &a) {
     constexpr int GROUPS = 32 / LANES;
@@ -223,27 +255,34 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
     const int sub = lane / LANES;
     const int warps_per_cta = blockDim.x >> 5;
     const int64_t warp_id = (int64_t)blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
-    const int64_t item_idx = warp_id * GROUPS + sub;
+    // A group walks the items  g, g + G, g + 2G, ...  (G = groups in the grid).  When the grid covers every item
+    // the loop runs once; a persistent grid (mggcn_tune "persist") makes several trips, and then the header of the
+    // item after next and the first (column, value) chunk of the next item are requested BEFORE the current item
+    // is worked on, so the two dependent loads at the start of an item (header -> index chunk) are off the critical
+    // path: short items (8 x 8 blocks at 8 GPUs, the column blocks of the 2-D schedule) are latency chains otherwise.
+    const int64_t groups_total = (int64_t)gridDim.x * warps_per_cta * GROUPS;
+    int64_t item_idx = warp_id * GROUPS + sub;
+    const uint64_t pol_b = a.policy ? make_policy_evict_last() : make_policy_normal();
+    const uint64_t pol_s = a.policy ? make_policy_evict_first() : make_policy_normal();
+    item_hdr cur = load_hdr(a, item_idx);
+    item_hdr nxt = load_hdr(a, item_idx + groups_total);
+    uint32_t c_first = GATHER ? a.g.own_lo : 0;
+    float v_first = 0.f;
+    if ((uint32_t)sl < cur.len) {
+        c_first = ldg_stream_u32(a.colidx + cur.begin + sl, pol_s);
+        v_first = ldg_stream_f32(a.vals + cur.begin + sl, pol_s);
+    }
+  for (int64_t wbase = warp_id * GROUPS; wbase < a.n_items; wbase += groups_total, item_idx += groups_total) {
     const bool valid = item_idx < a.n_items;
-
-    uint64_t begin = 0;
-    uint32_t len = 0, row = 0;
-    if (valid) {
-        if (a.items) {
-            const spmm_item it = a.items[item_idx];
-            begin = it.begin; len = it.len; row = it.row;
-        } else {
-            row = (uint32_t)item_idx;
-            if (a.rowptr64) {
-                const uint64_t *rp = static_cast<const uint64_t *>(a.rowptr);
-                begin = rp[row];
-                len = (uint32_t)(rp[row + 1] - begin);
-            } else {
-                const uint32_t *rp = static_cast<const uint32_t *>(a.rowptr);
-                begin = rp[row];
-                len = rp[row + 1] - (uint32_t)begin;
-            }
-        }
+    const uint64_t begin = cur.begin;
+    const uint32_t len = cur.len, row = cur.row;
+    // requests for the trips to come (no-ops past the end of the list)
+    const item_hdr nn = load_hdr(a, item_idx + 2 * groups_total);
+    uint32_t c_pre = GATHER ? a.g.own_lo : 0;
+    float v_pre = 0.f;
+    if ((uint32_t)sl < nxt.len) {
+        c_pre = ldg_stream_u32(a.colidx + nxt.begin + sl, pol_s);
+        v_pre = ldg_stream_f32(a.vals + nxt.begin + sl, pol_s);
     }
     // warp-uniform trip count (groups in one warp hold items of similar length: the plan sorts)
     uint32_t maxlen = len;
@@ -251,8 +290,6 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
 #pragma unroll
         for (int o = 16; o >= LANES; o >>= 1) maxlen = max(maxlen, __shfl_xor_sync(0xffffffffu, maxlen, o));
     }
-    const uint64_t pol_b = a.policy ? make_policy_evict_last() : make_policy_normal();
-    const uint64_t pol_s = a.policy ? make_policy_evict_first() : make_policy_normal();
     const uint32_t *ci = a.colidx + begin;
     const float *va = a.vals + begin;
     const bool is_segment = valid && item_idx < a.n_seg;
@@ -267,16 +304,32 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
             for (int e = 0; e < VEC; ++e) acc[k][e] = 0.f;
         }
         const float *Bl = a.B + f0 + VEC * sl;
+        // beta != 0 (every launch but the first of a staged / blocked accumulation): the old value of C is requested
+        // now and arrives while the row is gathered, instead of costing a DRAM round trip after the last FMA
+        float *crow = a.C + (int64_t)row * a.ldc;
+        float4 oldv[NCH];
+        if constexpr (VEC == 4) {
+#pragma unroll
+            for (int k = 0; k < NCH; ++k) {
+                oldv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                const int col0 = f0 + 4 * (sl + LANES * k);
+                if (valid && !is_segment && a.beta != 0.f && colok[k] && (EXACT || col0 + 3 < a.F))
+                    oldv[k] = *reinterpret_cast<const float4 *>(crow + col0);
+            }
+        }
 
-        uint32_t c_cur = GATHER ? a.g.own_lo : 0, c_nxt = 0;
-        float v_cur = 0.f, v_nxt = 0.f;
+        uint32_t c_cur = c_first, c_nxt = 0;
+        float v_cur = v_first, v_nxt = 0.f;
         // GATHER: the blocks of stages [0, ready] are in place; they cover the cyclic column interval
         // [own_lo, own_lo + g_len) of the gather buffer (own block first, then blocks rank+1, ... cyclically)
         int ready = 0;
         uint32_t g_len = GATHER ? a.g.own_n : 0;
-        if ((uint32_t)sl < len) {
-            c_cur = ldg_stream_u32(ci + sl, pol_s);
-            v_cur = ldg_stream_f32(va + sl, pol_s);
+        if (f0 > 0) {  // further passes over a row wider than the tile re-read its first chunk
+            c_cur = GATHER ? a.g.own_lo : 0; v_cur = 0.f;
+            if ((uint32_t)sl < len) {
+                c_cur = ldg_stream_u32(ci + sl, pol_s);
+                v_cur = ldg_stream_f32(va + sl, pol_s);
+            }
         }
         for (uint32_t pos = 0; pos < maxlen; pos += LANES) {
             const uint32_t npos = pos + LANES;
@@ -388,7 +441,6 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
             }
             continue;
         }
-        float *crow = a.C + (int64_t)row * a.ldc;
 #pragma unroll
         for (int k = 0; k < NCH; ++k) {
             if (!colok[k]) continue;
@@ -396,8 +448,7 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
             if constexpr (VEC == 4) {
                 if (EXACT || col0 + 3 < a.F) {
                     float out[4];
-                    float4 old = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (a.beta != 0.f) old = *reinterpret_cast<const float4 *>(crow + col0);
+                    const float4 old = oldv[k];
                     out[0] = a.alpha * acc[k][0] + (a.beta != 0.f ? a.beta * old.x : 0.f);
                     out[1] = a.alpha * acc[k][1] + (a.beta != 0.f ? a.beta * old.y : 0.f);
                     out[2] = a.alpha * acc[k][2] + (a.beta != 0.f ? a.beta * old.z : 0.f);
@@ -419,10 +470,13 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
             }
         }
     }
+    cur = nxt; nxt = nn;
+    c_first = c_pre; v_first = v_pre;
+  }
 }
 
 template <int LANES, int NCH, int VEC, int UNROLL, bool EXACT, bool GATHER = false>
-__global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
+__global__ void __launch_bounds__(256, 4) spmm_kernel(const spmm_args a) {
     spmm_body<LANES, NCH, VEC, UNROLL, EXACT, GATHER>(a);
 }
 // Adds the partial sums of every split row in segment order and finishes the row.
@@ -444,15 +498,188 @@ __global__ void spmm_fixup_kernel(const split_row *rows, int64_t n_split, const 
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Experiment (mggcn_tune("tma", 1)): the rows of B travel L2 -> shared memory through the
+// TMA unit (cp.async.bulk, one 1-D bulk copy per gathered row, mbarrier-paced) instead of LSU loads into
+// registers, so the L1TEX pipe that ncu shows at 88 % carries none of the gather stream.  One warp per item; a ring
+// of TS stages x TR rows per warp; lanes 0..TR-1 issue the copies of a stage (lane j the row of entry j), every lane
+// then reads its float4 of each landed row from shared memory (conflict-free: consecutive lanes, consecutive 16 B).
+// Exact widths only (F = 4 * LPR floats, LPR = 16 or 32 lanes per row; with LPR = 16 the two half-warps take
+// alternate rows and are added at the end).  Result: see DESIGN.md section 7 -- kept or dropped on the measurement.
+// ---------------------------------------------------------------------------------------------
+constexpr int TR = 8, TS = 4;
+
+__device__ __forceinline__ uint32_t tma_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+template <int LPR>
+__global__ void __launch_bounds__(128) spmm_tma_kernel(const spmm_args a) {
+    constexpr int RB = LPR * 16;      // bytes per row of B
+    constexpr int RP = 32 / LPR;      // rows a warp reads per shared-memory instruction
+    extern __shared__ __align__(128) uint8_t tma_smem[];
+    const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    uint8_t *ring = tma_smem + (size_t)wic * (TS * TR * RB);
+    const uint32_t ring_u32 = tma_smem_u32(ring);
+    const uint32_t bar0 = tma_smem_u32(tma_smem + (size_t)nw * (TS * TR * RB)) + (uint32_t)wic * TS * 8;
+    if (lane < TS) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u * lane));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncwarp();
+
+    const int64_t item_idx = (int64_t)blockIdx.x * nw + wic;
+    if (item_idx >= a.n_items) return;
+    uint64_t begin;
+    uint32_t len, row;
+    if (a.items) {
+        const spmm_item it = a.items[item_idx];
+        begin = it.begin; len = it.len; row = it.row;
+    } else {
+        row = (uint32_t)item_idx;
+        const uint32_t *rp = static_cast<const uint32_t *>(a.rowptr);
+        begin = rp[row];
+        len = rp[row + 1] - (uint32_t)begin;
+    }
+    const uint64_t pol_s = make_policy_evict_first();
+    const uint32_t *ci = a.colidx + begin;
+    const float *va = a.vals + begin;
+    // three register chunks of 32 (column, value) pairs: k (being consumed), k+1 (being issued), k+2 (in flight)
+    uint32_t c0 = 0, c1 = 0, c2 = 0;
+    float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+    auto load_chunk = [&](uint32_t k, uint32_t &c, float &v) {
+        const uint32_t e = 32u * k + lane;
+        c = 0; v = 0.f;
+        if (e < len) {
+            c = ldg_stream_u32(ci + e, pol_s);
+            v = ldg_stream_f32(va + e, pol_s);
+        }
+    };
+    load_chunk(0, c0, v0);
+    load_chunk(1, c1, v1);
+    load_chunk(2, c2, v2);
+    uint32_t kbase = 0;  // chunk held in c0 / v0
+    const uint32_t n_sub = (len + TR - 1) / TR;
+
+    auto issue = [&](uint32_t q) {
+        const uint32_t e0 = q * TR, stage = q % TS;
+        const uint32_t nvalid = min((uint32_t)TR, len - e0);
+        const uint32_t which = e0 / 32 - kbase;  // 0 or 1 (the issue pointer runs (TS-1)*TR = 24 entries ahead)
+        const uint32_t c = __shfl_sync(0xffffffffu, which == 0 ? c0 : (which == 1 ? c1 : c2), (e0 + lane) & 31);
+        const uint32_t bar = bar0 + 8u * stage;
+        if (lane == 0)
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(nvalid * (uint32_t)RB) : "memory");
+        __syncwarp();
+        if ((uint32_t)lane < nvalid) {
+            const float *src = a.B + (int64_t)c * a.ldb;
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(ring_u32 + (stage * TR + lane) * RB), "l"(src), "r"((uint32_t)RB), "r"(bar)
+                         : "memory");
+        }
+    };
+
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (uint32_t q = 0; q < (uint32_t)(TS - 1) && q < n_sub; ++q) issue(q);
+    for (uint32_t q = 0; q < n_sub; ++q) {
+        if (q + TS - 1 < n_sub) issue(q + TS - 1);
+        const uint32_t stage = q % TS, parity = (q / TS) & 1u, bar = bar0 + 8u * stage;
+        uint32_t done = 0;
+        while (!done) {
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t}"
+                : "=r"(done)
+                : "r"(bar), "r"(parity)
+                : "memory");
+        }
+        const uint32_t e0 = q * TR;
+        const uint32_t which = e0 / 32 - kbase;
+        const float4 *rows = reinterpret_cast<const float4 *>(ring + (size_t)stage * TR * RB);
+        float4 x[TR / RP];
+#pragma unroll
+        for (int j = 0; j < TR / RP; ++j) x[j] = rows[(j * RP + lane / LPR) * LPR + (lane % LPR)];
+        __syncwarp();  // every lane has read the stage: the next issue may overwrite it
+#pragma unroll
+        for (int j = 0; j < TR / RP; ++j) {
+            const uint32_t e = e0 + j * RP + lane / LPR;
+            float v = __shfl_sync(0xffffffffu, which == 0 ? v0 : v1, e & 31);
+            if (e < len) {
+                acc[0] = fmaf(v, x[j].x, acc[0]); acc[1] = fmaf(v, x[j].y, acc[1]);
+                acc[2] = fmaf(v, x[j].z, acc[2]); acc[3] = fmaf(v, x[j].w, acc[3]);
+            }
+        }
+        if (((e0 + TR) & 31u) == 0) {  // the consumer leaves chunk kbase: rotate and prefetch chunk kbase + 3
+            c0 = c1; v0 = v1; c1 = c2; v1 = v2;
+            ++kbase;
+            load_chunk(kbase + 2, c2, v2);
+        }
+    }
+    if (RP == 2) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
+        if (lane >= 16) return;
+    }
+    const int col0 = 4 * (lane % LPR);
+    if (item_idx < a.n_seg) {
+        *reinterpret_cast<float4 *>(a.partial + item_idx * a.ldp + col0) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        return;
+    }
+    float *crow = a.C + (int64_t)row * a.ldc;
+    float4 old = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.beta != 0.f) old = *reinterpret_cast<const float4 *>(crow + col0);
+    float out[4] = {a.alpha * acc[0] + (a.beta != 0.f ? a.beta * old.x : 0.f), a.alpha * acc[1] + (a.beta != 0.f ? a.beta * old.y : 0.f),
+                    a.alpha * acc[2] + (a.beta != 0.f ? a.beta * old.z : 0.f), a.alpha * acc[3] + (a.beta != 0.f ? a.beta * old.w : 0.f)};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) out[e] = apply_epilogue(out[e], a.epi, row, col0 + e);
+    *reinterpret_cast<float4 *>(crow + col0) = make_float4(out[0], out[1], out[2], out[3]);
+}
+
 thread_local char t_last_config[256] = "";
+
+template <int LPR>
+int launch_tma(cudaStream_t st, const spmm_args &a) {
+    constexpr int threads = 128, nw = threads / 32;
+    constexpr size_t smem = (size_t)nw * TS * TR * LPR * 16 + (size_t)nw * TS * 8;
+    static std::atomic<bool> attr_set[64];
+    int dev = 0;
+    MGGCN_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
+        MGGCN_CUDA_TRY(cudaFuncSetAttribute(spmm_tma_kernel<LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
+    }
+    const int64_t grid = (a.n_items + nw - 1) / nw;
+    if (grid <= 0) return MGGCN_OK;
+    if (grid > 0x7fffffffll) return fail(MGGCN_E_UNSUPPORTED, "SpMM grid too large");
+    spmm_tma_kernel<LPR><<<(unsigned)grid, threads, smem, st>>>(a);
+    MGGCN_LAUNCH_CHECK();
+    snprintf(t_last_config, sizeof t_last_config, "spmm_tma_kernel<%d> (rows of B through cp.async.bulk, %d stages x %d rows per warp) grid=%u cta=%d F=%d",
+             LPR, TS, TR, (unsigned)grid, threads, a.F);
+    return MGGCN_OK;
+}
+
+int sm_count() {
+    static int v = [] {
+        int dev = 0, n = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) {
+            cudaGetLastError();
+            n = 148;
+        }
+        return n;
+    }();
+    return v;
+}
+// average entries per item of this launch (set by the dispatcher from the plan / matrix; < 0: unknown)
+thread_local double t_avg_len = -1.0;
+double avg_len_hint(const spmm_args &) { return t_avg_len < 0 ? 1e9 : t_avg_len; }
 
 template <int LANES, int NCH, int VEC>
 int launch_cfg(cudaStream_t st, const spmm_args &a) {
     constexpr int GROUPS = 32 / LANES;
     const int threads = g_threads;
     const int64_t items_per_cta = (int64_t)(threads / 32) * GROUPS;
-    const int64_t grid = (a.n_items + items_per_cta - 1) / items_per_cta;
+    int64_t grid = (a.n_items + items_per_cta - 1) / items_per_cta;
     if (grid <= 0) return MGGCN_OK;
+    // persistent form: as many CTAs as stay resident (63 registers -> 1024 threads per SM), every group walks the
+    // item list with a stride and prefetches the next item's header and first index chunk (see spmm_body)
+    const bool persist = g_persist == 1 || (g_persist == 0 && a.n_items > 0 && !a.g.flags && avg_len_hint(a) < 96.0);
+    if (persist) grid = std::min<int64_t>(grid, (int64_t)sm_count() * (1024 / threads) * std::max(1, g_persist_waves));
     if (grid > 0x7fffffffll) return fail(MGGCN_E_UNSUPPORTED, "SpMM grid too large");
     constexpr int U4 = LANES < 4 ? LANES : 4;
     const bool exact = a.F % (LANES * NCH * VEC) == 0;
@@ -470,8 +697,8 @@ int launch_cfg(cudaStream_t st, const spmm_args &a) {
         else spmm_kernel<LANES, NCH, VEC, U4, false><<<gr, threads, 0, st>>>(a);
     }
     MGGCN_LAUNCH_CHECK();
-    snprintf(t_last_config, sizeof t_last_config, "spmm_kernel<%d,%d,%d,%d,%s%s> grid=%u cta=%d F=%d", LANES, NCH, VEC, unroll,
-             exact ? "exact" : "ragged", a.g.flags ? ",gathered" : "", gr, threads, a.F);
+    snprintf(t_last_config, sizeof t_last_config, "spmm_kernel<%d,%d,%d,%d,%s%s> grid=%u%s cta=%d F=%d", LANES, NCH, VEC, unroll,
+             exact ? "exact" : "ragged", a.g.flags ? ",gathered" : "", gr, persist ? " (persistent)" : "", threads, a.F);
     return MGGCN_OK;
 }
 
@@ -490,6 +717,7 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
     if (plan && plan->rows != rows) return fail(MGGCN_E_INVALID, "plan was built for %lld rows, got %lld",
                                                (long long)plan->rows, (long long)rows);
     if (plan && !pb) pb = &plan->blk[0];
+    t_avg_len = plan && pb->n_items > 0 ? (double)pb->nnz / (double)pb->n_items : -1.0;
     spmm_args a{};
     a.items = plan ? plan->d_items + pb->first_item : nullptr;
     a.n_items = plan ? pb->n_items : rows;
@@ -534,7 +762,9 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
                          (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
                          (reinterpret_cast<uintptr_t>(ws) & 15) == 0;
     int rc;
-    if (aligned) {
+    if (g_tma && aligned && !gather && !rowptr64 && (F == 128 || F == 64) && (ldb * 4) % 16 == 0) {
+        rc = F == 128 ? launch_tma<32>(st, a) : launch_tma<16>(st, a);
+    } else if (aligned) {
         if (F4 <= 2) rc = launch_cfg<2, 1, 4>(st, a);
         else if (F4 <= 4) rc = launch_cfg<4, 1, 4>(st, a);
         else if (F4 <= 8) rc = launch_cfg<8, 1, 4>(st, a);
@@ -660,6 +890,7 @@ plan_block build_block(int64_t rows, int split_nnz, bool keep_empty, beg_fn beg,
     whole.reserve((size_t)rows);
     for (int64_t r = 0; r < rows; ++r) {
         const uint64_t l = len(r);
+        pb.nnz += (int64_t)l;
         if (l > (uint64_t)split_nnz) {
             const uint64_t nseg = (l + split_nnz - 1) / split_nnz;
             const uint64_t seg = (l + nseg - 1) / nseg;
@@ -896,6 +1127,9 @@ int mggcn_tune(const char *key, int value) {
     else if (!strcmp(key, "split")) slot = &g_split;
     else if (!strcmp(key, "slices")) slot = &g_slices;
     else if (!strcmp(key, "blocks")) slot = &g_blocks;
+    else if (!strcmp(key, "tma")) slot = &g_tma;
+    else if (!strcmp(key, "persist")) slot = &g_persist;
+    else if (!strcmp(key, "persist_waves")) slot = &g_persist_waves;
     else if (!strcmp(key, "window")) slot = &g_window;
     else if (!strcmp(key, "tile_mb")) slot = &g_tile_mb;
     else if (!strcmp(key, "gemm_tc")) slot = &mggcn::g_gemm_tc;

@@ -333,7 +333,10 @@ ORC_API void orc_init_weights(int64_t rows, int64_t cols, float gain, float *out
         x = (16807ull * x) % 2147483647ull;
         float canon = (float)(x - 1) / range;
         if (canon >= 1.0f) canon = nextafterf(1.0f, 0.0f);
-        out[i] = canon * (b - a) + a;
+        /* uniform_real_distribution: canonical * (b - a) + a, contracted into ONE fma by g++ -O3 on any
+         * FMA-capable target (how the reference is built: -march=native; oracle/_ref: -march=x86-64-v3);
+         * verified bit for bit against the reference build's W / b dumps (tests/test_ref_layers.py) */
+        out[i] = fmaf(canon, b - a, a);
     }
 }
 

@@ -375,3 +375,37 @@ def test_row_pointers_past_2_to_32(mg, orc, cuda):
         check(Ct.cpu().numpy(), want, absrow)
     del big_ci, big_va
     torch.cuda.empty_cache()
+
+
+@pytest.mark.parametrize("F", [128, 64])
+@pytest.mark.parametrize("use_plan", [False, True])
+def test_tma_gather_variant_matches_oracle(mg, orc, cuda, F, use_plan):
+    """mggcn_tune("tma", 1): rows of B travel through cp.async.bulk into shared memory (experiment of VERDICT r1
+    item 6a).  Same contract as the default kernel: alpha/beta, split rows, fused epilogue, empty rows, ragged tails
+    of every length modulo the 8-row stage and the 32-entry register chunk."""
+    torch = cuda
+    rng = np.random.default_rng(F + use_plan)
+    n, m = 1100, 900
+    rp, ci, va = random_csr(rng, n, m, 37, heavy=3)
+    B = rng.standard_normal((m, F)).astype(np.float32)
+    C0 = rng.standard_normal((n, F)).astype(np.float32)
+    bias = rng.standard_normal(F).astype(np.float32)
+    base = orc.spmm(rp, ci, va, B, C_in=C0.copy(), alpha=0.5, beta=2.0, acc64=True)
+    want = np.where(base + bias > 0, base + bias, 0.01 * (base + bias))
+    absrow = orc.spmm(rp, ci, np.abs(va), np.abs(B), acc64=True).max(1) * 0.5 + 2 * np.abs(C0).max(1) + 2
+    rpt, cit, vat = to_dev(torch, rp, ci, va)
+    Bt, bt = torch.from_numpy(B).cuda(), torch.from_numpy(bias).cuda()
+    plan = mg.SpmmPlan(rp.astype(np.uint32), split_nnz=300) if use_plan else None
+    old = mg.lib().mggcn_tune(b"tma", 1)
+    try:
+        Ct = torch.from_numpy(C0).cuda()
+        mg.spmm(rpt, cit, vat, Bt, Ct, cols=m, F=F, alpha=0.5, beta=2.0, epi=mg.make_epilogue(mg.EPI_LEAKY_RELU, 0.01, bias=bt), plan=plan)
+        assert "spmm_tma_kernel" in mg.lib().mggcn_last_spmm_config().decode()
+        check(Ct.cpu().numpy(), want, absrow)
+        Cn = torch.full((n, F), float("nan"), device="cuda")
+        mg.spmm(rpt, cit, vat, Bt, Cn, cols=m, F=F, plan=plan)
+        got = Cn.cpu().numpy()
+        assert np.isfinite(got).all() and np.all(got[1] == 0.0)
+        check(got, orc.spmm(rp, ci, va, B, acc64=True), absrow)
+    finally:
+        mg.lib().mggcn_tune(b"tma", old)

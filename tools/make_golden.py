@@ -33,7 +33,10 @@ int main() {
 """ % (gain_expr, rows, cols)
     with tempfile.TemporaryDirectory() as d:
         open(os.path.join(d, "a.cpp"), "w").write(src)
-        subprocess.check_call(["g++", "-O1", "-o", os.path.join(d, "a"), os.path.join(d, "a.cpp")])
+        # same flags as the reference build in oracle/Makefile (the reference's CMake uses -O3 -march=native): on an
+        # FMA target g++ contracts the distribution's  canonical * (b - a) + a  into one fused multiply-add, and those
+        # are the values the reference binary starts from (checked against its W / b dumps, tests/test_ref_layers.py)
+        subprocess.check_call(["g++", "-std=c++20", "-O3", "-march=x86-64-v3", "-o", os.path.join(d, "a"), os.path.join(d, "a.cpp")])
         return [float(x) for x in subprocess.check_output([os.path.join(d, "a")]).split()]
 
 

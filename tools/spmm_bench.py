@@ -94,6 +94,9 @@ def main():
     ap.add_argument("--gathered", type=int, default=0, help="P: time rank 0's block row as ONE gathered launch (flags preset), "
                     "as one plain launch with global columns, and as P staged launches")
     ap.add_argument("--tune", nargs="*", default=[], help="key=value knobs passed to mggcn_tune")
+    ap.add_argument("--variants", nargs="*", default=[], help="named knob sets timed one after the other, each "
+                    "'tag:key=value,key=value' (knobs are restored afterwards); a 'blocks=' knob rebuilds the plan as a "
+                    "column-blocked one, e.g.  base:  tma:tma=1,slices=1  2d:blocks=7,window=32")
     ap.add_argument("--unroll", type=int, default=4)
     ap.add_argument("--threads", type=int, default=64)
     args = ap.parse_args()
@@ -152,6 +155,24 @@ def main():
                     mg.spmm(rpt, cit, vat, B[:, i * w:(i + 1) * w], Cm[:, i * w:(i + 1) * w], cols=m, F=w, plan=plan)
             med, mn = timeit(sliced)
             report("ours-sliced", med, mn, slices=k)
+        for spec in args.variants:
+            tag, _, kvs = spec.partition(":")
+            knobs = dict(kv.split("=") for kv in kvs.split(",") if kv)
+            saved = {k: mg.lib().mggcn_tune(k.encode(), int(v)) for k, v in knobs.items()}
+            try:
+                pl = plan
+                if "blocks" in knobs:
+                    pl = mg.SpmmPlan(AT.rowptr.astype(np.uint32), colidx_host=AT.colidx, cols=m, F_hint=F)
+                fn = lambda: mg.spmm(rpt, cit, vat, B, Cm, cols=m, F=F, plan=pl)
+                fn()
+                cfg = mg.lib().mggcn_last_spmm_config().decode()
+                med, mn = timeit(fn)
+                report("variant-" + tag, med, mn, knobs=knobs, config=cfg, plan_blocks=pl.blocks)
+                ref_plain = mg.spmm(rpt, cit, vat, B, torch.empty_like(Cm), cols=m, F=F, plan=None)
+                print(json.dumps({"tag": "variant-" + tag, "max_abs_diff_vs_plain": float((ref_plain[:, :F] - Cm[:, :F]).abs().max())}), flush=True)
+            finally:
+                for k, v in saved.items():
+                    mg.lib().mggcn_tune(k.encode(), v)
         if args.cusparse:
             S = torch.sparse_csr_tensor(rpt.to(torch.int32), cit, vat, size=(n, m))
             Bc = B[:, :F].contiguous()
