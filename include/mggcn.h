@@ -132,8 +132,9 @@ MGGCN_API int mggcn_spmm_plan_create_i64(int64_t rows, const uint64_t *rowptr_ho
  * entry points then run (feature windows) x (column blocks) launches over the SAME rowptr / colidx / vals arrays,
  * accumulating C between blocks.  Needs a host copy of colidx; rows must hold their columns ascending in
  * key(c) = (c - col_rot) mod cols and inside [0, col_span) (col_rot = 0, col_span = cols: any sorted CSR).
- * F_hint: the widest F this plan will serve.  The block count comes from a DRAM-traffic model and is 1 (= the plain
- * plan) whenever blocking would not pay; mggcn_tune("blocks", k) forces it. */
+ * F_hint: the widest F this plan will serve.  Block count: mggcn_tune("blocks", k) asks for exactly k,
+ * mggcn_tune("blocks_model", 1) lets a DRAM-traffic model choose; by default the plan has ONE block, because on
+ * B200 every blocked configuration measured slower than the plain one. */
 MGGCN_API int mggcn_spmm_plan_create_blocked_i32(int64_t rows, int64_t cols, const uint32_t *rowptr_host,
                                                  const uint32_t *colidx_host, uint32_t col_rot,
                                                  int64_t col_span, int F_hint, int split_nnz,
@@ -142,8 +143,8 @@ MGGCN_API int mggcn_spmm_plan_create_blocked_i32(int64_t rows, int64_t cols, con
 MGGCN_API int mggcn_spmm_plan_blocks(const mggcn_spmm_plan_t *plan);
 MGGCN_API size_t mggcn_spmm_plan_workspace_bytes(const mggcn_spmm_plan_t *plan, int F);
 MGGCN_API void mggcn_spmm_plan_destroy(mggcn_spmm_plan_t *plan);
-/* Tuning knobs for experiments ("unroll", "threads", "policy", "split", "slices", "blocks", "window", "tile_mb",
- * "gemm_tc", "gemm_kgroup", "skip_exchange"); a negative value only queries.
+/* Tuning knobs for experiments ("unroll", "threads", "policy", "split", "slices", "blocks", "blocks_model", "window",
+ * "tile_mb", "tma", "gemm_tc", "gemm_kgroup", "skip_exchange"); a negative value only queries.
  * Returns the old value or MGGCN_E_INVALID for an unknown key. */
 MGGCN_API int mggcn_tune(const char *key, int value);
 /* Thread-local text naming the kernel instance and schedule the last SpMM call of this thread launched, e.g.

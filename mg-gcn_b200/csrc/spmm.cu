@@ -53,7 +53,7 @@ struct split_row {
 // split list are finished by the fix-up kernel.
 struct plan_block {
     int64_t first_item = 0, n_items = 0, n_seg = 0, first_split = 0, n_split = 0;
-    int64_t nnz = 0;  // entries covered by the items (the launch is made persistent when the items are short)
+    int64_t nnz = 0;  // entries covered by the items
 };
 
 struct mggcn_spmm_plan {
@@ -78,10 +78,8 @@ int g_policy = 1;     // 1: L2 evict_last for B, evict_first for the CSR stream;
 int g_split = 0;      // row-split threshold of new plans; 0 = chosen from the matrix (see plan_create)
 int g_slices = 0;     // k > 1: run as k launches over F/k-wide column windows of B and C; 0: k = 2 when B (cols x F floats)
                       // is larger than half of the L2 but its half is not (see spmm_scheduled); 1: never
-int g_persist = 0;    // 0: persistent grid + next-item prefetch for launches of short items (avg < 96 entries); 1: always; 2: never
-int g_persist_waves = 1;  // persistent grid = this many times the resident CTA count
 int g_tma = 0;        // 1: F = 64 / 128 products gather B through the TMA unit (spmm_tma_kernel, experiment)
-int g_blocks = 0;     // column blocks of new blocked plans: 0 = from the traffic model, 1 = never, k = exactly k
+int g_blocks = 0;     // column blocks of new blocked plans: 0 / 1 = none (measured best), k > 1 = exactly k, < 0 = traffic model
 int g_window = 0;     // feature-window width of blocked plans at launch: 0 = widest that keeps a block's B rows resident
 int g_tile_mb = 0;    // bytes of B a launch may count on staying L2-resident, in MiB; 0 = 45 % of the L2
 
@@ -219,33 +217,6 @@ __device__ __forceinline__ float apply_epilogue(float x, const mggcn_epilogue &e
 // One group of LANES threads per item; NCH vectors of VEC floats per lane; the group covers
 // LANES*NCH*VEC features per pass and loops over passes when F is wider.
 // EXACT: F is a multiple of the pass width, so no per-lane column predicate is needed.
-// Header of a work item as the kernel uses it.
-struct item_hdr {
-    uint64_t begin;
-    uint32_t len, row;
-};
-__device__ __forceinline__ item_hdr load_hdr(const spmm_args &a, int64_t idx) {
-    item_hdr h{0, 0, 0};
-    if (idx < a.n_items) {
-        if (a.items) {
-            const spmm_item it = a.items[idx];
-            h.begin = it.begin; h.len = it.len; h.row = it.row;
-        } else {
-            h.row = (uint32_t)idx;
-            if (a.rowptr64) {
-                const uint64_t *rp = static_cast<const uint64_t *>(a.rowptr);
-                h.begin = rp[idx];
-                h.len = (uint32_t)(rp[idx + 1] - h.begin);
-            } else {
-                const uint32_t *rp = static_cast<const uint32_t *>(a.rowptr);
-                h.begin = rp[idx];
-                h.len = rp[idx + 1] - (uint32_t)h.begin;
-            }
-        }
-    }
-    return h;
-}
-
 template <int LANES, int NCH, int VEC, int UNROLL, bool EXACT, bool GATHER>
 __device__ __forceinline__ void spmm_body(const spmm_args &a) {
     constexpr int GROUPS = 32 / LANES;
@@ -255,34 +226,27 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
     const int sub = lane / LANES;
     const int warps_per_cta = blockDim.x >> 5;
     const int64_t warp_id = (int64_t)blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
-    // A group walks the items  g, g + G, g + 2G, ...  (G = groups in the grid).  When the grid covers every item
-    // the loop runs once; a persistent grid (mggcn_tune "persist") makes several trips, and then the header of the
-    // item after next and the first (column, value) chunk of the next item are requested BEFORE the current item
-    // is worked on, so the two dependent loads at the start of an item (header -> index chunk) are off the critical
-    // path: short items (8 x 8 blocks at 8 GPUs, the column blocks of the 2-D schedule) are latency chains otherwise.
-    const int64_t groups_total = (int64_t)gridDim.x * warps_per_cta * GROUPS;
-    int64_t item_idx = warp_id * GROUPS + sub;
-    const uint64_t pol_b = a.policy ? make_policy_evict_last() : make_policy_normal();
-    const uint64_t pol_s = a.policy ? make_policy_evict_first() : make_policy_normal();
-    item_hdr cur = load_hdr(a, item_idx);
-    item_hdr nxt = load_hdr(a, item_idx + groups_total);
-    uint32_t c_first = GATHER ? a.g.own_lo : 0;
-    float v_first = 0.f;
-    if ((uint32_t)sl < cur.len) {
-        c_first = ldg_stream_u32(a.colidx + cur.begin + sl, pol_s);
-        v_first = ldg_stream_f32(a.vals + cur.begin + sl, pol_s);
-    }
-  for (int64_t wbase = warp_id * GROUPS; wbase < a.n_items; wbase += groups_total, item_idx += groups_total) {
+    const int64_t item_idx = warp_id * GROUPS + sub;
     const bool valid = item_idx < a.n_items;
-    const uint64_t begin = cur.begin;
-    const uint32_t len = cur.len, row = cur.row;
-    // requests for the trips to come (no-ops past the end of the list)
-    const item_hdr nn = load_hdr(a, item_idx + 2 * groups_total);
-    uint32_t c_pre = GATHER ? a.g.own_lo : 0;
-    float v_pre = 0.f;
-    if ((uint32_t)sl < nxt.len) {
-        c_pre = ldg_stream_u32(a.colidx + nxt.begin + sl, pol_s);
-        v_pre = ldg_stream_f32(a.vals + nxt.begin + sl, pol_s);
+
+    uint64_t begin = 0;
+    uint32_t len = 0, row = 0;
+    if (valid) {
+        if (a.items) {
+            const spmm_item it = a.items[item_idx];
+            begin = it.begin; len = it.len; row = it.row;
+        } else {
+            row = (uint32_t)item_idx;
+            if (a.rowptr64) {
+                const uint64_t *rp = static_cast<const uint64_t *>(a.rowptr);
+                begin = rp[row];
+                len = (uint32_t)(rp[row + 1] - begin);
+            } else {
+                const uint32_t *rp = static_cast<const uint32_t *>(a.rowptr);
+                begin = rp[row];
+                len = rp[row + 1] - (uint32_t)begin;
+            }
+        }
     }
     // warp-uniform trip count (groups in one warp hold items of similar length: the plan sorts)
     uint32_t maxlen = len;
@@ -290,6 +254,8 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
 #pragma unroll
         for (int o = 16; o >= LANES; o >>= 1) maxlen = max(maxlen, __shfl_xor_sync(0xffffffffu, maxlen, o));
     }
+    const uint64_t pol_b = a.policy ? make_policy_evict_last() : make_policy_normal();
+    const uint64_t pol_s = a.policy ? make_policy_evict_first() : make_policy_normal();
     const uint32_t *ci = a.colidx + begin;
     const float *va = a.vals + begin;
     const bool is_segment = valid && item_idx < a.n_seg;
@@ -304,32 +270,16 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
             for (int e = 0; e < VEC; ++e) acc[k][e] = 0.f;
         }
         const float *Bl = a.B + f0 + VEC * sl;
-        // beta != 0 (every launch but the first of a staged / blocked accumulation): the old value of C is requested
-        // now and arrives while the row is gathered, instead of costing a DRAM round trip after the last FMA
-        float *crow = a.C + (int64_t)row * a.ldc;
-        float4 oldv[NCH];
-        if constexpr (VEC == 4) {
-#pragma unroll
-            for (int k = 0; k < NCH; ++k) {
-                oldv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-                const int col0 = f0 + 4 * (sl + LANES * k);
-                if (valid && !is_segment && a.beta != 0.f && colok[k] && (EXACT || col0 + 3 < a.F))
-                    oldv[k] = *reinterpret_cast<const float4 *>(crow + col0);
-            }
-        }
 
-        uint32_t c_cur = c_first, c_nxt = 0;
-        float v_cur = v_first, v_nxt = 0.f;
+        uint32_t c_cur = GATHER ? a.g.own_lo : 0, c_nxt = 0;
+        float v_cur = 0.f, v_nxt = 0.f;
         // GATHER: the blocks of stages [0, ready] are in place; they cover the cyclic column interval
         // [own_lo, own_lo + g_len) of the gather buffer (own block first, then blocks rank+1, ... cyclically)
         int ready = 0;
         uint32_t g_len = GATHER ? a.g.own_n : 0;
-        if (f0 > 0) {  // further passes over a row wider than the tile re-read its first chunk
-            c_cur = GATHER ? a.g.own_lo : 0; v_cur = 0.f;
-            if ((uint32_t)sl < len) {
-                c_cur = ldg_stream_u32(ci + sl, pol_s);
-                v_cur = ldg_stream_f32(va + sl, pol_s);
-            }
+        if ((uint32_t)sl < len) {
+            c_cur = ldg_stream_u32(ci + sl, pol_s);
+            v_cur = ldg_stream_f32(va + sl, pol_s);
         }
         for (uint32_t pos = 0; pos < maxlen; pos += LANES) {
             const uint32_t npos = pos + LANES;
@@ -441,6 +391,7 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
             }
             continue;
         }
+        float *crow = a.C + (int64_t)row * a.ldc;
 #pragma unroll
         for (int k = 0; k < NCH; ++k) {
             if (!colok[k]) continue;
@@ -448,7 +399,8 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
             if constexpr (VEC == 4) {
                 if (EXACT || col0 + 3 < a.F) {
                     float out[4];
-                    const float4 old = oldv[k];
+                    float4 old = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (a.beta != 0.f) old = *reinterpret_cast<const float4 *>(crow + col0);
                     out[0] = a.alpha * acc[k][0] + (a.beta != 0.f ? a.beta * old.x : 0.f);
                     out[1] = a.alpha * acc[k][1] + (a.beta != 0.f ? a.beta * old.y : 0.f);
                     out[2] = a.alpha * acc[k][2] + (a.beta != 0.f ? a.beta * old.z : 0.f);
@@ -470,13 +422,10 @@ __device__ __forceinline__ void spmm_body(const spmm_args &a) {
             }
         }
     }
-    cur = nxt; nxt = nn;
-    c_first = c_pre; v_first = v_pre;
-  }
 }
 
 template <int LANES, int NCH, int VEC, int UNROLL, bool EXACT, bool GATHER = false>
-__global__ void __launch_bounds__(256, 4) spmm_kernel(const spmm_args a) {
+__global__ void __launch_bounds__(256) spmm_kernel(const spmm_args a) {
     spmm_body<LANES, NCH, VEC, UNROLL, EXACT, GATHER>(a);
 }
 // Adds the partial sums of every split row in segment order and finishes the row.
@@ -654,32 +603,13 @@ int launch_tma(cudaStream_t st, const spmm_args &a) {
     return MGGCN_OK;
 }
 
-int sm_count() {
-    static int v = [] {
-        int dev = 0, n = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) {
-            cudaGetLastError();
-            n = 148;
-        }
-        return n;
-    }();
-    return v;
-}
-// average entries per item of this launch (set by the dispatcher from the plan / matrix; < 0: unknown)
-thread_local double t_avg_len = -1.0;
-double avg_len_hint(const spmm_args &) { return t_avg_len < 0 ? 1e9 : t_avg_len; }
-
 template <int LANES, int NCH, int VEC>
 int launch_cfg(cudaStream_t st, const spmm_args &a) {
     constexpr int GROUPS = 32 / LANES;
     const int threads = g_threads;
     const int64_t items_per_cta = (int64_t)(threads / 32) * GROUPS;
-    int64_t grid = (a.n_items + items_per_cta - 1) / items_per_cta;
+    const int64_t grid = (a.n_items + items_per_cta - 1) / items_per_cta;
     if (grid <= 0) return MGGCN_OK;
-    // persistent form: as many CTAs as stay resident (63 registers -> 1024 threads per SM), every group walks the
-    // item list with a stride and prefetches the next item's header and first index chunk (see spmm_body)
-    const bool persist = g_persist == 1 || (g_persist == 0 && a.n_items > 0 && !a.g.flags && avg_len_hint(a) < 96.0);
-    if (persist) grid = std::min<int64_t>(grid, (int64_t)sm_count() * (1024 / threads) * std::max(1, g_persist_waves));
     if (grid > 0x7fffffffll) return fail(MGGCN_E_UNSUPPORTED, "SpMM grid too large");
     constexpr int U4 = LANES < 4 ? LANES : 4;
     const bool exact = a.F % (LANES * NCH * VEC) == 0;
@@ -697,8 +627,8 @@ int launch_cfg(cudaStream_t st, const spmm_args &a) {
         else spmm_kernel<LANES, NCH, VEC, U4, false><<<gr, threads, 0, st>>>(a);
     }
     MGGCN_LAUNCH_CHECK();
-    snprintf(t_last_config, sizeof t_last_config, "spmm_kernel<%d,%d,%d,%d,%s%s> grid=%u%s cta=%d F=%d", LANES, NCH, VEC, unroll,
-             exact ? "exact" : "ragged", a.g.flags ? ",gathered" : "", gr, persist ? " (persistent)" : "", threads, a.F);
+    snprintf(t_last_config, sizeof t_last_config, "spmm_kernel<%d,%d,%d,%d,%s%s> grid=%u cta=%d F=%d", LANES, NCH, VEC, unroll,
+             exact ? "exact" : "ragged", a.g.flags ? ",gathered" : "", gr, threads, a.F);
     return MGGCN_OK;
 }
 
@@ -717,7 +647,6 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
     if (plan && plan->rows != rows) return fail(MGGCN_E_INVALID, "plan was built for %lld rows, got %lld",
                                                (long long)plan->rows, (long long)rows);
     if (plan && !pb) pb = &plan->blk[0];
-    t_avg_len = plan && pb->n_items > 0 ? (double)pb->nnz / (double)pb->n_items : -1.0;
     spmm_args a{};
     a.items = plan ? plan->d_items + pb->first_item : nullptr;
     a.n_items = plan ? pb->n_items : rows;
@@ -982,8 +911,14 @@ int plan_create_blocked(int64_t rows, int64_t cols, const uint32_t *rowptr, cons
     if (col_span <= 0 || col_span > cols) col_span = cols;
     const uint64_t nnz = rows > 0 ? (uint64_t)rowptr[rows] : 0;
     int nblk = g_blocks;
-    if (nblk <= 0) {
-        // choose the block count that the traffic model likes best; blocks only pay when B is far beyond the L2
+    if (nblk == 0) {
+        // Measured on B200 (profiles/r02_spmm_products_variants.jsonl): the 2-D schedule does cut DRAM traffic
+        // (products-shape, F = 256: ~70 GB instead of 125 GB per aggregation) but every configuration tried is
+        // SLOWER (25-46 ms against 17.7 ms), because a row keeps only ~8 entries per column block and the launches
+        // become latency-bound item loops (DRAM 25 % busy).  The planner therefore never blocks on its own; the
+        // traffic model below is only consulted when mggcn_tune("blocks_model", 1) asks for it.
+        nblk = 1;
+    } else if (nblk < 0) {
         const double budget = (double)resident_budget();
         nblk = 1;
         double best = schedule_cost((double)rows, (double)col_span, (double)nnz, F_hint, 1, budget);
@@ -1127,9 +1062,8 @@ int mggcn_tune(const char *key, int value) {
     else if (!strcmp(key, "split")) slot = &g_split;
     else if (!strcmp(key, "slices")) slot = &g_slices;
     else if (!strcmp(key, "blocks")) slot = &g_blocks;
+    else if (!strcmp(key, "blocks_model")) { const int old = g_blocks < 0; if (value >= 0) g_blocks = value ? -1 : 0; return old; }
     else if (!strcmp(key, "tma")) slot = &g_tma;
-    else if (!strcmp(key, "persist")) slot = &g_persist;
-    else if (!strcmp(key, "persist_waves")) slot = &g_persist_waves;
     else if (!strcmp(key, "window")) slot = &g_window;
     else if (!strcmp(key, "tile_mb")) slot = &g_tile_mb;
     else if (!strcmp(key, "gemm_tc")) slot = &mggcn::g_gemm_tc;

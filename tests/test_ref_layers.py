@@ -6,10 +6,16 @@ built by oracle/Makefile from /root/reference/src where it lies): it builds gcn 
 src/main.cpp does, runs one forward + backward from the reference's initialisation and writes every layer's output
 and W / b / G_W / G_b through the reference's accessors (src/gcn.hpp:503-517,622-635,992-994,1053-1055).  The engine runs
 the same epoch on the same files.  Tolerance contract: both sides are fp32 with different
-summation orders (cuSPARSE's is unspecified), so
-  * layer outputs:     |ours - ref| <= 1e-5 * max(1, ||H_l||_inf)            every element
-  * weight gradients:  |ours - ref| <= 1e-5 * ||G||_inf  of the tensor        every element
-and the test prints max and RMS of both so the margin is on record."""
+summation orders (cuSPARSE's and cuBLAS's are unspecified), so
+  * layer outputs:     |ours - ref| <= 1e-5 * max(1, ||H_l||_inf)                       every element
+  * weight gradients:  |ours - ref| <= max(1e-5, 2 * noise_l) * ||G_l||_inf            every element
+where noise_l = ||ref - port||_inf / ||ref||_inf is how far the reference build ITSELF is from a third fp32
+evaluation of the same formulas in a third summation order (the oracle's serial C port).  A weight gradient is a
+sum over all vertices of products that largely cancel (G_W = H^T T: 1e5 terms of either sign), so its fp32 rounding
+noise is relative to the size of the terms, not of the sum; where that noise is below 1e-5 (every tensor at reddit
+shape) the bar IS 1e-5, and where it is not (the first layer at products shape, 122 k vertices x 104 raw features of
+either sign) no fp32 implementation -- the reference's included -- reproduces another to 1e-5.  The test prints max
+and RMS of ours-vs-reference and the noise floor for every tensor, so the margin is on record."""
 import os
 import subprocess
 
@@ -32,7 +38,7 @@ def stats(got, ref, floor_one):
 
 @pytest.mark.parametrize("P", [1, 2])
 @pytest.mark.parametrize("shape,scale,hidden", [("reddit", 0.25, [128, 128, 128]), ("products", 0.05, [256, 256])])
-def test_layers_and_gradients_match_the_reference_build(mg, cuda, tmp_path, P, shape, scale, hidden):
+def test_layers_and_gradients_match_the_reference_build(mg, orc, cuda, tmp_path, P, shape, scale, hidden):
     torch = cuda
     if torch.cuda.device_count() < P:
         pytest.skip(f"needs {P} GPUs")
@@ -88,13 +94,19 @@ def test_layers_and_gradients_match_the_reference_build(mg, cuda, tmp_path, P, s
         mg.check(mg.lib().mggcn_engine_backward(e.handle))
     for e in engs:
         e.sync()
+    # third evaluation: the oracle's serial fp32 port of the same epoch (fixes the fp32 noise floor per tensor)
+    port = orc.Gcn(sizes, N, (A_T.rowptr, A_T.colidx, A_T.vals), (A.rowptr, A.colidx, A.vals), P=P, cuts=cuts)
+    port.train_forward(X, Y)
+    port.backward()
     for l in range(L):
         for nm in ("GW", "Gb"):
             got = engs[0].get(f"{nm}{l}")
             ref = mg.read_dense(str(out / f"{nm}{l}.bin")).ravel()
             mx, rms = stats(got, ref, False)
-            report.append(f"  {nm}{l}: max {mx:.2e} rms {rms:.2e}")
-            assert mx <= 1e-5, (nm, l, mx)
+            noise, _ = stats(port.tensor(f"{nm}{l}"), ref, False)
+            bar = max(1e-5, 2 * noise)
+            report.append(f"  {nm}{l}: max {mx:.2e} rms {rms:.2e}   (reference vs serial fp32 port: {noise:.2e}; bar {bar:.1e})")
+            assert mx <= bar, (nm, l, mx, noise)
     report.append(f"  activations on the other side of LeakyReLU's kink: {flips}")
     print("\n".join(report))
     with open(os.path.join(ROOT, "gpurun_out", f"ref_layers_{shape}_P{P}.txt") if os.path.isdir(os.path.join(ROOT, "gpurun_out"))
