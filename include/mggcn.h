@@ -187,6 +187,9 @@ MGGCN_API int mggcn_broadcast_rows_f32(mggcn_stream_t stream, const float *row, 
                                        size_t rows, size_t m, int discard);
 MGGCN_API int mggcn_axpy_f32(mggcn_stream_t stream, size_t n, float alpha, const float *x,
                              float *y);
+/* y = alpha * x + beta * y   (src/cuda_utils.cu:81-87; the SGD step of linear::update, src/gcn.hpp:141-144) */
+MGGCN_API int mggcn_axpby_f32(mggcn_stream_t stream, size_t n, float alpha, const float *x, float beta,
+                              float *y);
 
 /* ------------------------------------------------------------------------------------------
  * N2. Fused row-softmax + cross-entropy + argmax + gradient, in place on the logits

@@ -85,6 +85,7 @@ _SIGS = {
     "mggcn_leaky_relu_backward_f32": (C.c_int, [_vp, _vp, _vp, _vp, _sz, _f32]),
     "mggcn_broadcast_rows_f32": (C.c_int, [_vp, _vp, _vp, _sz, _sz, _i32]),
     "mggcn_axpy_f32": (C.c_int, [_vp, _sz, _f32, _vp, _vp]),
+    "mggcn_axpby_f32": (C.c_int, [_vp, _sz, _f32, _vp, _f32, _vp]),
     "mggcn_softmax_xent_f32": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _vp, _f32, _vp, _vp, _sz]),
     "mggcn_softmax_xent_workspace_bytes": (_sz, [_i64]),
     "mggcn_adam_f32": (C.c_int, [_vp, _sz, _vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _f32, _f32, _f32, _sz]),

@@ -361,6 +361,11 @@ __global__ void axpy_kernel(size_t n, float alpha, const float *x, float *y) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
         y[i] = fmaf(alpha, x[i], y[i]);
 }
+// y = alpha * x + beta * y   (axpby of src/cuda_utils.cu:81-87: the SGD step and Adam's first moment)
+__global__ void axpby_kernel(size_t n, float alpha, const float *x, float beta, float *y) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        y[i] = alpha * x[i] + beta * y[i];
+}
 unsigned ew_grid(size_t n) { return (unsigned)std::max<size_t>(1, std::min<size_t>((n + 255) / 256, 148 * 16)); }
 
 // ------------------------------------------------------------------------------------------------
@@ -554,6 +559,14 @@ int mggcn_axpy_f32(mggcn_stream_t stream, size_t n, float alpha, const float *x,
     if (!n) return MGGCN_OK;
     if (!x || !y) return fail(MGGCN_E_INVALID, "null operand");
     axpy_kernel<<<ew_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(n, alpha, x, y);
+    MGGCN_LAUNCH_CHECK();
+    return MGGCN_OK;
+}
+
+int mggcn_axpby_f32(mggcn_stream_t stream, size_t n, float alpha, const float *x, float beta, float *y) {
+    if (!n) return MGGCN_OK;
+    if (!x || !y) return fail(MGGCN_E_INVALID, "null operand");
+    axpby_kernel<<<ew_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(n, alpha, x, beta, y);
     MGGCN_LAUNCH_CHECK();
     return MGGCN_OK;
 }

@@ -78,6 +78,7 @@ int g_policy = 1;     // 1: L2 evict_last for B, evict_first for the CSR stream;
 int g_split = 0;      // row-split threshold of new plans; 0 = chosen from the matrix (see plan_create)
 int g_slices = 0;     // k > 1: run as k launches over F/k-wide column windows of B and C; 0: k = 2 when B (cols x F floats)
                       // is larger than half of the L2 but its half is not (see spmm_scheduled); 1: never
+int g_narrow = 0;     // lane mapping for 9..16 float4 per row, see spmm_dispatch
 int g_tma = 0;        // 1: F = 64 / 128 products gather B through the TMA unit (spmm_tma_kernel, experiment)
 int g_blocks = 0;     // column blocks of new blocked plans: 0 / 1 = none (measured best), k > 1 = exactly k, < 0 = traffic model
 int g_window = 0;     // feature-window width of blocked plans at launch: 0 = widest that keeps a block's B rows resident
@@ -697,6 +698,10 @@ int spmm_dispatch(cudaStream_t st, int64_t rows, int64_t cols, const void *rowpt
         if (F4 <= 2) rc = launch_cfg<2, 1, 4>(st, a);
         else if (F4 <= 4) rc = launch_cfg<4, 1, 4>(st, a);
         else if (F4 <= 8) rc = launch_cfg<8, 1, 4>(st, a);
+        // class widths (41 -> 44, 47 -> 48 floats = 11 / 12 float4): 16 lanes leave 5 / 4 of them idle on every
+        // gather; "narrow" = 1: 4 lanes x 3 float4 (8 rows per warp, no idle lane), 2: 8 lanes x 2 float4
+        else if (F4 > 8 && F4 <= 12 && g_narrow == 1) rc = launch_cfg<4, 3, 4>(st, a);
+        else if (F4 > 8 && F4 <= 16 && g_narrow == 2) rc = launch_cfg<8, 2, 4>(st, a);
         else if (F4 <= 16) rc = launch_cfg<16, 1, 4>(st, a);
         else if (F4 <= 32) rc = launch_cfg<32, 1, 4>(st, a);
         else rc = launch_cfg<32, 2, 4>(st, a);
@@ -1064,6 +1069,7 @@ int mggcn_tune(const char *key, int value) {
     else if (!strcmp(key, "blocks")) slot = &g_blocks;
     else if (!strcmp(key, "blocks_model")) { const int old = g_blocks < 0; if (value >= 0) g_blocks = value ? -1 : 0; return old; }
     else if (!strcmp(key, "tma")) slot = &g_tma;
+    else if (!strcmp(key, "narrow")) slot = &g_narrow;
     else if (!strcmp(key, "window")) slot = &g_window;
     else if (!strcmp(key, "tile_mb")) slot = &g_tile_mb;
     else if (!strcmp(key, "gemm_tc")) slot = &mggcn::g_gemm_tc;
