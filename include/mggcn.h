@@ -144,7 +144,9 @@ MGGCN_API int mggcn_spmm_plan_blocks(const mggcn_spmm_plan_t *plan);
 MGGCN_API size_t mggcn_spmm_plan_workspace_bytes(const mggcn_spmm_plan_t *plan, int F);
 MGGCN_API void mggcn_spmm_plan_destroy(mggcn_spmm_plan_t *plan);
 /* Tuning knobs for experiments ("unroll", "threads", "policy", "split", "slices", "blocks", "blocks_model", "window",
- * "tile_mb", "tma", "gemm_tc", "gemm_kgroup", "skip_exchange"); a negative value only queries.
+ * "tile_mb", "tma", "narrow", "gemm_tc", "gemm_kgroup", "skip_exchange", "xstreams" = streams a peer block is split
+ * over, "xpull" = SM-driven peer pulls, "h2d_sm" = CTAs reading pinned inputs instead of a copy-engine transfer);
+ * a negative value only queries.
  * Returns the old value or MGGCN_E_INVALID for an unknown key. */
 MGGCN_API int mggcn_tune(const char *key, int value);
 /* Thread-local text naming the kernel instance and schedule the last SpMM call of this thread launched, e.g.

@@ -282,9 +282,10 @@ SHAPES = {
     "reddit": (232965, 114615892, 602, 41, 1, 2.6, 21657),
     "products": (2449029, 123718280, 100, 47, 1, 2.9, 17481),
     "proteins": (132534, 79122504, 8, 112, 0, 0.0, 0),
-    # uniform-random neighbours and no vertex permutation: every rank walks the whole sample stream (1.6 B pairs) to
-    # build its slab, and the power-law sampler's random table look-ups per endpoint would make that minutes per rank
-    "papers100M": (111059956, 3231371744, 128, 172, 0, 0.0, 0),
+    # degree model 2 (union of k = 14 affine bijections of Z_n and their inverses, csrc/host_gen.cpp): uniform
+    # degrees, a row costs O(k) on whichever rank builds it.  Walking a global sample stream (models 0 / 1) costs
+    # every rank 1.6 G samples here -- minutes per rank with 4 host threads each.
+    "papers100M": (111059956, 3231371744, 128, 172, 2, 0.0, 0),
 }
 # shapes whose generator output needs no balancing permutation (uniform degrees)
 UNPERMUTED = {"papers100M"}

@@ -66,7 +66,7 @@ template <typename x_t, typename v_t, typename r_t>
 void matmul(dist_context ctx, const dist_row_csr_matrix<x_t, v_t, r_t> &A, dist_row_dn_matrix<r_t> B,
             const dist_row_dn_matrix<r_t> &C, const std::vector<cuda_ptr<char>> &ext_buffer,
             std::vector<dist_row_dn_matrix<r_t>> B_bcast, const r_t alpha, const r_t beta, const std::string name = "",
-            spmm_alg_t alg = SPMM_ALG_DEFAULT) {
+            spmm_alg_t alg = SPMM_ALG_DEFAULT, const mggcn_epilogue *epi = nullptr) {
     const std::size_t P = ctx.size();
     const int comm = ctx.bcast_stream_id();
     const std::size_t nbuf = B_bcast.size();
@@ -84,7 +84,7 @@ void matmul(dist_context ctx, const dist_row_csr_matrix<x_t, v_t, r_t> &A, dist_
         ctx.record(sn + "_matmul-spmm-start", 0);
         for (std::size_t j = 0; j < P; ++j)
             matmul(ctx[j], A[{j, i}], B_bcast[i % nbuf][j], C[j], j < ext_buffer.size() ? ext_buffer[j] : none, alpha,
-                   i == 0 ? beta : (r_t)1, alg);
+                   i == 0 ? beta : (r_t)1, alg, i + 1 == P ? epi : nullptr);  // the epilogue sees the complete sum
         ctx.record(sn + "_matmul-spmm", 0);
         ctx.register_timer(si + "_matmul-bcast", si + "_matmul-bcast-start", si + "_matmul-bcast-finish");
         ctx.register_timer(sn + "_matmul-spmm-stage", sn + "_matmul-spmm-start", sn + "_matmul-spmm");
@@ -132,10 +132,16 @@ inline void matmul(const dist_context &ctx, const dist_row_dn_matrix<float> &A, 
     for (std::size_t i = 0; i < ctx.size(); ++i) matmul(ctx[i], A[i], B[i], C[i], alpha, beta, false, B_T);
 }
 
-// y += alpha * x   (cublasSaxpy, src/cuda_utils.hpp:326-334)
-inline void axpy(const context &ctx, const float alpha, const dn_matrix<float> &x, const dn_matrix<float> &y) {
+// y += alpha * x   (cublasSaxpy, src/cuda_utils.hpp:326-342; same argument order)
+inline void axpy(const context &ctx, const dn_matrix<float> &x, const dn_matrix<float> &y, const float alpha) {
     ctx.set();
     CHECK_MGGCN(mggcn_axpy_f32(ctx.stream(0), x.size(), alpha, x.buffer(), y.buffer()));
+}
+
+// y = alpha * x + beta * y   (src/cuda_utils.cu:81-87, wrapper src/cuda_utils.hpp:336-344)
+inline void axpby(const context &ctx, const dn_matrix<float> &x, const dn_matrix<float> &y, const float alpha, const float beta) {
+    ctx.set();
+    CHECK_MGGCN(mggcn_axpby_f32(ctx.stream(0), x.size(), alpha, x.buffer(), beta, y.buffer()));
 }
 
 // out = max(in, alpha * in)   (src/cuda_utils.cu:26-31, wrapper src/cuda_utils.hpp:470-483)

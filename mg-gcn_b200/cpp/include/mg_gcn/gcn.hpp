@@ -1,6 +1,7 @@
 // gcn.hpp -- the aggregation functors (the drop-in boundary of the hot path), the loss layer and
-// the model classes.  Surface of the reference's src/gcn.hpp:13-86 (sparse_linear,
-// dist_sparse_linear), :769-823,872-935 (softmax cross-entropy), :937-1056 (gcn, dist_gcn).
+// the layer and model classes.  Surface of the reference's src/gcn.hpp:13-86 (sparse_linear,
+// dist_sparse_linear), :88-296,411-637 (linear, gcn_layer and their dist forms: gcn_layers.hpp),
+// :769-823,872-935 (softmax cross-entropy), :937-1056 (gcn, dist_gcn: gcn_model.hpp).
 #pragma once
 
 #include "cuda_utils.hpp"
@@ -19,10 +20,10 @@ class sparse_linear {
    public:
     sparse_linear(const std::string &name, csr_t A, csr_t A_T) : name(name), A(std::move(A)), A_T(std::move(A_T)) {}
 
-    // C = A B (discard) or C += A B
-    void operator()(context ctx, const dn_t &B, const dn_t &C, bool discard = true) {
+    // C = A B (discard) or C += A B; `epi` (optional) is applied to the sum before its only store
+    void operator()(context ctx, const dn_t &B, const dn_t &C, bool discard = true, const mggcn_epilogue *epi = nullptr) {
         ctx.record(name + "0_matmul-spmm-start", 0);
-        matmul(ctx, A, B, C, ext_buffer, (r_t)1, discard ? (r_t)0 : (r_t)1);
+        matmul(ctx, A, B, C, ext_buffer, (r_t)1, discard ? (r_t)0 : (r_t)1, SPMM_ALG_DEFAULT, epi);
         ctx.record(name + "0_matmul-spmm-finish", 0);
         ctx.register_timer(name + "0_matmul-spmm", name + "0_matmul-spmm-start", name + "0_matmul-spmm-finish");
     }
@@ -62,9 +63,10 @@ class dist_sparse_linear {
         : name(name), A(std::move(A)), A_T(std::move(A_T)), bcast_buffer(std::move(bcast_buffer)),
           bcast_buffer2(std::move(bcast_buffer2)) {}
 
-    void operator()(const dist_context &ctx, const dn_t &B, const dn_t &C, bool discard = true) {
+    void operator()(const dist_context &ctx, const dn_t &B, const dn_t &C, bool discard = true,
+                    const mggcn_epilogue *epi = nullptr) {
         if (B_bcast.empty() || B_bcast[0].m() != B.m()) B_bcast = staging(ctx, B);
-        matmul(ctx, A, B, C, ext_buffer, B_bcast, (r_t)1, discard ? (r_t)0 : (r_t)1, name + "0_");
+        matmul(ctx, A, B, C, ext_buffer, B_bcast, (r_t)1, discard ? (r_t)0 : (r_t)1, name + "0_", SPMM_ALG_DEFAULT, epi);
     }
     void backward(const dist_context &ctx, const dn_t &G, const dn_t &G_out, bool discard = true) {
         if (G_bcast.empty() || G_bcast[0].m() != G.m()) G_bcast = staging(ctx, G);
@@ -112,4 +114,5 @@ class softmax_cross_entropy_loss {
 
 }  // namespace mg_gcn
 
+#include "gcn_layers.hpp"
 #include "gcn_model.hpp"

@@ -177,6 +177,9 @@ int main(int argc, char **argv) {
         layer_tests(ctx, false);
         layer_tests(ctx, true);
         model_test(ctx);
+        linear_test(ctx);
+        layers_test(ctx, {64, 32});  // every layer transforms first
+        layers_test(ctx, {96, 32});  // layer 0 aggregates first (in < out): quirk Q2 path
     } else if (mode == "dist") {
         int n = 0;
         if (cudaGetDeviceCount(&n) != cudaSuccess || n < 2) {

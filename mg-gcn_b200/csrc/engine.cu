@@ -34,6 +34,12 @@ namespace mggcn {
 // launches stay).  The result is wrong by construction -- it exists to MEASURE how much of an epoch the exchange
 // leaves exposed: exposed = epoch(with copies) - epoch(without).  Never set outside a measurement.
 int g_skip_exchange = 0;
+// exchange tuning: a block's pull is cut into g_xstreams row ranges issued on as many streams (one copy engine each);
+// g_xpull = 1 moves the bytes with pull_copy_kernel (SM loads over NVLink) instead of the copy engines
+int g_xstreams = 2;
+int g_xpull = 0;
+// > 0: set_inputs reads pinned host rows with that many CTAs of pull_copy_kernel instead of a copy-engine transfer
+int g_h2d_sm = 0;
 void spmm_touched_cols_hint(int64_t n);
 int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx,
                   const float *vals, float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
@@ -286,6 +292,9 @@ struct mggcn_engine {
     std::vector<int64_t> sizes;
     std::vector<layer_t> layers;
     cudaStream_t sc = nullptr, sm = nullptr, scopy = nullptr;
+    static constexpr int kXStreams = 4;
+    cudaStream_t sx[kXStreams] = {nullptr};      // extra exchange streams: sx[0] is sm itself
+    cudaEvent_t ev_xfork = nullptr, ev_xjoin[kXStreams] = {nullptr};
     ncclComm_t comm = nullptr;
 
     adj_block adj[2][kMaxRanks];
@@ -339,7 +348,7 @@ struct mggcn_engine {
     // graph
     cudaGraphExec_t graph_exec = nullptr;
     float g_lr = 0, g_b1 = 0, g_b2 = 0, g_wd = 0, g_eps = 0;
-    int g_skip = 0;
+    int g_skip = 0, g_xs = 0, g_xp = 0;
     int64_t launches_per_epoch = 0;
     bool forward_done = false;
 
@@ -407,6 +416,41 @@ int xbarrier(eng *e, cudaStream_t st) {
     return MGGCN_OK;
 }
 
+// One block of a peer's B into `dst`, ordered on the exchange stream e->sm.  The block is cut into g_xstreams
+// row ranges that travel on separate streams (a copy-engine transfer is one engine's work however large it is;
+// two engines pulling halves of the block roughly double the NVLink rate a rank sees): fork from e->sm, join
+// back into it, so the caller's events and barriers on e->sm cover every part.
+int peer_pull(eng *e, int blk, size_t off, float *dst, size_t rows, size_t ld) {
+    if (g_skip_exchange) return MGGCN_OK;  // measurement only
+    const char *src = e->peer_arena[blk] + off;
+    const bool by_sm = g_xpull || (e->peer_inproc[blk] && !e->capturing);
+    int nx = std::min(g_xstreams, (int)mggcn_engine::kXStreams);
+    nx = std::max(1, std::min(nx, (int)(rows / 1024) + 1));
+    if (e->sm == e->sc || by_sm) nx = 1;  // no overlap: everything on the compute stream; SM pulls fill the link alone
+    if (nx > 1) MGGCN_CUDA_TRY(cudaEventRecord(e->ev_xfork, e->sm));
+    for (int i = nx - 1; i >= 0; --i) {
+        const size_t r_lo = rows * (size_t)i / nx, r_hi = rows * (size_t)(i + 1) / nx;
+        const size_t count = (r_hi - r_lo) * ld;
+        if (!count) continue;
+        cudaStream_t st = i == 0 ? e->sm : e->sx[i];
+        if (i > 0) MGGCN_CUDA_TRY(cudaStreamWaitEvent(st, e->ev_xfork, 0));
+        const float *s_ = reinterpret_cast<const float *>(src) + r_lo * ld;
+        float *d_ = dst + r_lo * ld;
+        if (by_sm) {
+            // count is a multiple of 4 floats (ld is), both ends are 16-byte aligned (256-byte arena carvings, ld % 4 == 0)
+            pull_copy_kernel<<<64, 512, 0, st>>>(reinterpret_cast<const float4 *>(s_), reinterpret_cast<float4 *>(d_), count / 4);
+            MGGCN_LAUNCH_CHECK();
+        } else {
+            MGGCN_CUDA_TRY(cudaMemcpyAsync(d_, s_, count * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        }
+        if (i > 0) {
+            MGGCN_CUDA_TRY(cudaEventRecord(e->ev_xjoin[i], st));
+            MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->sm, e->ev_xjoin[i], 0));
+        }
+    }
+    return MGGCN_OK;
+}
+
 // C = A_which[rank][:] * B  (+ epilogue), B and C are this rank's row blocks (n x ld).
 // P stages with a double-buffered exchange; src/cuda_utils.hpp:57-92.
 int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggcn_epilogue *epi,
@@ -438,19 +482,9 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
             const adj_block &a = e->adj[which][g];
             for (int s = std::max(1, e->groups[g].first); s < e->groups[g].second; ++s) {
                 const int blk = (e->rank + s) % P;
-                const size_t count = ((size_t)e->cuts[blk + 1] - (size_t)e->cuts[blk]) * (size_t)ld;
                 float *dst = e->gather + (size_t)e->cuts[blk] * (size_t)ld;
                 TRY(timer_begin(e, tname + std::to_string(s) + "_matmul-bcast", e->sm, &t_x));
-                if (g_skip_exchange) {
-                    // measurement only: see g_skip_exchange
-                } else if (e->peer_inproc[blk] && !e->capturing) {
-                    pull_copy_kernel<<<64, 512, 0, e->sm>>>(reinterpret_cast<const float4 *>(e->peer_arena[blk] + off),
-                                                            reinterpret_cast<float4 *>(dst), count / 4);
-                    MGGCN_LAUNCH_CHECK();
-                } else {
-                    MGGCN_CUDA_TRY(cudaMemcpyAsync(dst, e->peer_arena[blk] + off, count * sizeof(float),
-                                                   cudaMemcpyDeviceToDevice, e->sm));
-                }
+                TRY(peer_pull(e, blk, off, dst, (size_t)e->cuts[blk + 1] - (size_t)e->cuts[blk], (size_t)ld));
                 TRY(timer_end(e, e->sm, t_x));
             }
             if (g > 0 && e->sm != e->sc) {
@@ -560,17 +594,7 @@ int dist_spmm(eng *e, int which, const float *B, float *C, int64_t F, const mggc
             const size_t count = (size_t)a.cols * (size_t)ld;
             TRY(timer_begin(e, tname + std::to_string(s) + "_matmul-bcast", e->sm, &t_x));
             if (e->p2p) {
-                if (g_skip_exchange) {
-                    // measurement only: see g_skip_exchange
-                } else if (e->peer_inproc[blk] && !e->capturing) {
-                    // count is a multiple of 4 floats (ld is), both ends are 256-byte aligned arena carvings
-                    pull_copy_kernel<<<64, 512, 0, e->sm>>>(reinterpret_cast<const float4 *>(e->peer_arena[blk] + off),
-                                                            reinterpret_cast<float4 *>(e->stage[s & 1]), count / 4);
-                    MGGCN_LAUNCH_CHECK();
-                } else {
-                    MGGCN_CUDA_TRY(cudaMemcpyAsync(e->stage[s & 1], e->peer_arena[blk] + off, count * sizeof(float),
-                                                   cudaMemcpyDeviceToDevice, e->sm));
-                }
+                TRY(peer_pull(e, blk, off, e->stage[s & 1], (size_t)a.cols, (size_t)ld));
                 src = e->stage[s & 1];
                 TRACE(e->rank, "dist_spmm: peer copy enqueued");
             } else if (blk == e->rank) {
@@ -839,6 +863,14 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     if (e->overlap && e->P > 1) E_CUDA(cudaStreamCreateWithPriority(&e->sm, cudaStreamNonBlocking, hi));
     else e->sm = e->sc;
     E_CUDA(cudaStreamCreateWithFlags(&e->scopy, cudaStreamNonBlocking));
+    e->sx[0] = e->sm;
+    if (e->sm != e->sc) {
+        E_CUDA(cudaEventCreateWithFlags(&e->ev_xfork, cudaEventDisableTiming));
+        for (int i = 1; i < mggcn_engine::kXStreams; ++i) {
+            E_CUDA(cudaStreamCreateWithPriority(&e->sx[i], cudaStreamNonBlocking, hi));
+            E_CUDA(cudaEventCreateWithFlags(&e->ev_xjoin[i], cudaEventDisableTiming));
+        }
+    }
     E_CUDA(cudaEventCreateWithFlags(&e->ev_ready, cudaEventDisableTiming));
     E_CUDA(cudaEventCreateWithFlags(&e->ev_done, cudaEventDisableTiming));
     E_CUDA(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
@@ -1125,6 +1157,19 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
 
 // host rows (pitch = width floats) into device rows of pitch ld: one flat copy when the pitches agree
 static int copy_rows_in(float *dst, int64_t ld, const float *src, int64_t width, int64_t rows, cudaStream_t st) {
+    if (g_h2d_sm && ld == width && ((size_t)rows * (size_t)width) % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        // pinned host memory is mapped into the device's address space: a few CTAs reading it with 128-bit loads
+        // keep PCIe full and leave the copy engines to the peer exchange (an H2D transfer and the pulls of an
+        // aggregation otherwise queue on the same engines, tune key "h2d_sm")
+        cudaPointerAttributes attr;
+        if (cudaPointerGetAttributes(&attr, src) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer) {
+            pull_copy_kernel<<<g_h2d_sm, 512, 0, st>>>(reinterpret_cast<const float4 *>(attr.devicePointer),
+                                                     reinterpret_cast<float4 *>(dst), (size_t)rows * (size_t)width / 4);
+            MGGCN_LAUNCH_CHECK();
+            return MGGCN_OK;
+        }
+        cudaGetLastError();
+    }
     if (ld == width) {
         MGGCN_CUDA_TRY(cudaMemcpyAsync(dst, src, (size_t)rows * (size_t)width * 4, cudaMemcpyDefault, st));
     } else {
@@ -1252,7 +1297,7 @@ int mggcn_engine_adam_update(mggcn_engine_t *e, float lr, float beta1, float bet
 // its first barrier until its peers are launched too).
 static int ensure_graph(mggcn_engine_t *e, float lr, float beta1, float beta2, float wd, float eps) {
     if (e->graph_exec && (lr != e->g_lr || beta1 != e->g_b1 || beta2 != e->g_b2 || wd != e->g_wd || eps != e->g_eps ||
-                          e->g_skip != g_skip_exchange)) {
+                          e->g_skip != g_skip_exchange || e->g_xs != g_xstreams || e->g_xp != g_xpull)) {
         cudaGraphExecDestroy(e->graph_exec);
         e->graph_exec = nullptr;
     }
@@ -1292,6 +1337,8 @@ static int ensure_graph(mggcn_engine_t *e, float lr, float beta1, float beta2, f
     MGGCN_CUDA_TRY(cudaStreamSynchronize(e->sc));
     e->g_lr = lr; e->g_b1 = beta1; e->g_b2 = beta2; e->g_wd = wd; e->g_eps = eps;
     e->g_skip = g_skip_exchange;
+    e->g_xs = g_xstreams;
+    e->g_xp = g_xpull;
     return MGGCN_OK;
 }
 
@@ -1492,6 +1539,11 @@ void mggcn_engine_destroy(mggcn_engine_t *e) {
     if (e->sm && e->sm != e->sc) cudaStreamDestroy(e->sm);
     if (e->sc) cudaStreamDestroy(e->sc);
     if (e->scopy) cudaStreamDestroy(e->scopy);
+    for (int i = 1; i < mggcn_engine::kXStreams; ++i) {
+        if (e->sx[i]) cudaStreamDestroy(e->sx[i]);
+        if (e->ev_xjoin[i]) cudaEventDestroy(e->ev_xjoin[i]);
+    }
+    if (e->ev_xfork) cudaEventDestroy(e->ev_xfork);
     cudaGetLastError();
     delete e;
 }

@@ -77,6 +77,73 @@ struct alias_table {
 
 }  // namespace
 
+// degree_model 2 -- the union of k affine bijections of Z_n and their inverses: the neighbours of u are
+// a_j*u + b_j and a_j^-1 * (u - b_j) (mod n_raw), j < k = floor(directed edges / 2n), plus the self-loop.  The
+// pattern is symmetric by construction and a row costs O(k) whichever rank builds it: no walk over a global sample
+// stream (3.2 G samples per rank at papers100M-shape took minutes), nothing to exchange.  Every vertex has degree
+// <= 2k + 1 (uniform like model 0's expectation); the multipliers are ~n-sized, so consecutive rows gather rows of B
+// that are far apart -- the same no-reuse access pattern as a random graph.
+static int gen_rows_affine(int64_t n_raw, int64_t n, int64_t target_directed_edges, uint64_t seed, int permute, int64_t r0,
+                           int64_t r1, mggcn_gen_t **out, int64_t *n_padded, int64_t *nnz) {
+    if (permute) return fail(MGGCN_E_UNSUPPORTED, "degree model 2 is generated unpermuted (its ids are already scattered)");
+    const int64_t nl = r1 - r0;
+    const int k = (int)std::max<int64_t>(1, target_directed_edges / (2 * n_raw));
+    const uint64_t m = (uint64_t)n_raw;
+    std::vector<uint64_t> a((size_t)k), ainv((size_t)k), b((size_t)k);
+    auto gcd = [](uint64_t x, uint64_t y) { while (y) { uint64_t t = x % y; x = y; y = t; } return x; };
+    for (int j = 0; j < k; ++j) {
+        uint64_t aj = m > 2 ? 2 + hash2(seed ^ 0x41464649ull, (uint64_t)j) % (m - 2) : 1;
+        while (gcd(aj, m) != 1) aj = aj + 1 < m ? aj + 1 : 1;
+        // inverse by the extended Euclidean algorithm (signed 128-bit: the coefficients stay below m)
+        __int128 t0 = 0, t1 = 1, r0e = (__int128)m, r1e = (__int128)aj;
+        while (r1e != 0) {
+            __int128 q = r0e / r1e, t2 = t0 - q * t1, r2 = r0e - q * r1e;
+            t0 = t1; t1 = t2; r0e = r1e; r1e = r2;
+        }
+        a[j] = aj;
+        ainv[j] = (uint64_t)((t0 % (__int128)m + (__int128)m) % (__int128)m);
+        b[j] = hash2(seed ^ 0x4F464653ull, (uint64_t)j) % m;
+    }
+    auto row = [&](int64_t u, uint32_t *buf) -> uint32_t {  // sorted, deduplicated, self-loop included
+        if (u >= n_raw) { buf[0] = (uint32_t)u; return 1; }  // padding vertex: isolated but for its self-loop
+        uint32_t c = 0;
+        for (int j = 0; j < k; ++j) {
+            const uint64_t v1 = (a[j] * (uint64_t)u + b[j]) % m;
+            const uint64_t v2 = ainv[j] * (((uint64_t)u + m - b[j]) % m) % m;
+            buf[c++] = (uint32_t)v1;
+            buf[c++] = (uint32_t)v2;
+        }
+        buf[c++] = (uint32_t)u;
+        std::sort(buf, buf + c);
+        return (uint32_t)(std::unique(buf, buf + c) - buf);
+    };
+    auto *g = new (std::nothrow) mggcn_gen;
+    if (!g) return fail(MGGCN_E_NOMEM, "out of memory");
+    g->n = nl;
+    g->rowptr.assign((size_t)nl + 1, 0);
+#pragma omp parallel
+    {
+        std::vector<uint32_t> buf((size_t)2 * k + 1);
+#pragma omp for schedule(static)
+        for (int64_t i = 0; i < nl; ++i) g->rowptr[i + 1] = row(r0 + i, buf.data());
+    }
+    for (int64_t i = 0; i < nl; ++i) g->rowptr[i + 1] += g->rowptr[i];
+    g->colidx.resize(g->rowptr[nl]);
+#pragma omp parallel
+    {
+        std::vector<uint32_t> buf((size_t)2 * k + 1);
+#pragma omp for schedule(static)
+        for (int64_t i = 0; i < nl; ++i) {
+            const uint32_t c = row(r0 + i, buf.data());
+            std::copy(buf.data(), buf.data() + c, g->colidx.data() + g->rowptr[i]);
+        }
+    }
+    *out = g;
+    *n_padded = n;
+    *nnz = (int64_t)g->rowptr[nl];
+    return MGGCN_OK;
+}
+
 // Rows [r0, r1) of the generated graph (r1 < 0: all of them).  The edge samples are counter-based, so a rank that
 // wants only its row block walks the same sample stream and keeps the pairs that touch its rows: the rows it builds
 // are entry for entry the rows of the whole graph.
@@ -92,6 +159,8 @@ static int gen_rows(int64_t n_raw, int64_t target_directed_edges, int degree_mod
     const uint32_t lo32 = (uint32_t)r0;
     auto mine = [&](uint32_t x) { return (uint64_t)x - lo32 < (uint64_t)nl; };
     const int64_t E = target_directed_edges / 2;  // undirected samples; each yields two entries
+
+    if (degree_model == 2) return gen_rows_affine(n_raw, n, target_directed_edges, seed, permute, r0, r1, out, n_padded, nnz);
 
     alias_table tab;
     if (degree_model == 1) {

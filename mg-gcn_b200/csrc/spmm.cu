@@ -33,6 +33,7 @@ using namespace mggcn;
 namespace mggcn {
 extern int g_gemm_tc, g_gemm_kgroup;  // gemm_tc.cu
 extern int g_skip_exchange;           // engine.cu
+extern int g_xstreams, g_xpull, g_h2d_sm;  // engine.cu
 }
 
 namespace {
@@ -1075,6 +1076,9 @@ int mggcn_tune(const char *key, int value) {
     else if (!strcmp(key, "gemm_tc")) slot = &mggcn::g_gemm_tc;
     else if (!strcmp(key, "gemm_kgroup")) slot = &mggcn::g_gemm_kgroup;
     else if (!strcmp(key, "skip_exchange")) slot = &mggcn::g_skip_exchange;
+    else if (!strcmp(key, "xstreams")) slot = &mggcn::g_xstreams;
+    else if (!strcmp(key, "xpull")) slot = &mggcn::g_xpull;
+    else if (!strcmp(key, "h2d_sm")) slot = &mggcn::g_h2d_sm;
     if (!slot) return fail(MGGCN_E_INVALID, "unknown tuning key %s", key);
     const int old = *slot;
     if (slot == &g_threads && (value < 32 || value > 256 || value % 32)) return fail(MGGCN_E_INVALID, "threads must be 32..256");

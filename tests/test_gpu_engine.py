@@ -160,7 +160,9 @@ def run_dist_check(cuda, world, port, *extra):
            "127.0.0.1", "--master-port", str(port), os.path.join(root, "tests", "dist_engine_check.py"), *extra]
     env = dict(os.environ, MGGCN_BARRIER_TIMEOUT_MS="5000")
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
-    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    # torchrun's own report fills the tail of stderr: pull the ranks' exception lines out in front of it
+    why = [l for l in r.stderr.splitlines() if "Error" in l or "assert" in l or "mggcn" in l][:20]
+    assert r.returncode == 0, "\n".join(why) + "\n" + r.stdout[-2000:] + r.stderr[-1500:]
     assert "dist check ok" in r.stdout
     return r.stdout
 
