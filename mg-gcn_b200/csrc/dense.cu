@@ -15,7 +15,7 @@ using namespace mggcn;
 namespace mggcn {
 // gemm_tc.cu: tcgen05 / TMEM / TMA form (3xTF32), used whenever the operands are 16-byte aligned
 bool gemm_tc_eligible(int64_t M, int64_t N, int64_t K, const float *A, int64_t lda, const float *B, int64_t ldb);
-size_t gemm_tc_workspace_bytes(int ta, int64_t M, int64_t N, int64_t K);
+size_t gemm_tc_workspace_bytes(int ta, int tb, int64_t M, int64_t N, int64_t K);
 int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, float alpha, const float *A, int64_t lda,
             const float *B, int64_t ldb, float beta, float *C, int64_t ldc, const mggcn_epilogue &epi, void *ws,
             size_t ws_bytes);
@@ -466,7 +466,7 @@ size_t mggcn_gemm_workspace_bytes(int ta, int tb, int64_t M, int64_t N, int64_t 
     (void)tb;
     const int nz = splitk_slices(ta, M, N, K);
     const size_t simt = nz > 1 ? (size_t)nz * (size_t)M * (size_t)N * sizeof(float) : 0;
-    return std::max(simt, gemm_tc_workspace_bytes(ta, M, N, K));
+    return std::max(simt, gemm_tc_workspace_bytes(ta, tb, M, N, K));
 }
 
 int mggcn_gemm_f32(mggcn_stream_t stream, int ta, int tb, int64_t M, int64_t N, int64_t K, float alpha,

@@ -37,6 +37,10 @@ using namespace mggcn;
 namespace mggcn {
 int g_gemm_tc = 1;       // 0: never use this path (mggcn_tune "gemm_tc")
 int g_gemm_kgroup = 2;   // k-blocks per tensor-core accumulation chain (mggcn_tune "gemm_kgroup")
+int g_gemm_split = 0;    // 0: hi = rna_tf32(x), lo = rna_tf32(x - hi);  1: hi = x with the low 13 mantissa bits cleared,
+                         //    lo = x - hi left as it is (the tensor core drops its low bits): a third of the ALU work
+int g_gemm_presplit = 1; // a small B operand (the weights of H*W and G*W^T) is split once per call into hi / lo arrays
+                         //    in the workspace and both halves arrive by TMA: the splitter warps only handle A
 }  // namespace mggcn
 
 namespace {
@@ -69,6 +73,8 @@ struct tc_args {
     int64_t kchunk;    // multiple of BK
     int mt, nt;        // tiles along M, N
     int kgroup;
+    int split_mode;    // g_gemm_split
+    int b_presplit;    // B's hi / lo come from mapB / mapBlo, nothing to split
     float alpha, beta;
     mggcn_epilogue epi;
 };
@@ -158,6 +164,35 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes,
     return d;
 }
 
+// x = hi + lo with hi a TF32 number.  Default: both halves rounded to nearest (dropped terms 2^-22 relative).
+// trunc: hi = x with the low 13 mantissa bits cleared, lo = x - hi exactly (<= 13 significant bits; the tensor core
+// uses its top 11): dropped terms 2^-20 relative, a third of the instructions.
+__device__ __forceinline__ void split_tf32(float x, float &h, float &l, bool trunc) {
+    if (trunc) {
+        h = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+        l = x - h;
+    } else {
+        uint32_t u;
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+        h = __uint_as_float(u);
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x - h));
+        l = __uint_as_float(u);
+    }
+}
+
+// B (rows x cols, pitch ldb) -> hi / lo arrays of pitch ld_out, pad columns zeroed
+__global__ void presplit_kernel(const float *__restrict__ B, int64_t ldb, int64_t rows, int64_t cols, float *__restrict__ hi,
+                                float *__restrict__ lo, int64_t ld_out, int trunc) {
+    const int64_t total = rows * ld_out;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / ld_out, c = i - r * ld_out;
+        float h = 0.f, l = 0.f;
+        if (c < cols) split_tf32(B[r * ldb + c], h, l, trunc != 0);
+        hi[i] = h;
+        lo[i] = l;
+    }
+}
+
 __device__ __forceinline__ float epi_apply(float x, const mggcn_epilogue &e, int64_t row, int64_t col, float bias) {
     x += bias;
     if (e.kind == MGGCN_EPI_LEAKY_RELU) {
@@ -177,7 +212,8 @@ __device__ __forceinline__ float epi_apply(float x, const mggcn_epilogue &e, int
 // ---------------------------------------------------------------------------------------------
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(NTHREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const tc_args g) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+               const __grid_constant__ CUtensorMap mapBlo, const tc_args g) {
     using C = cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -203,6 +239,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
+        if (g.b_presplit) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapBlo)) : "memory");
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < C::STAGES; ++s) {
@@ -245,7 +282,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 const int64_t kb0 = z * kb_per_z, kb1 = min(kb_all, kb0 + kb_per_z);
                 for (int64_t kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(bar_empty(s), ph ^ 1u);
-                    mbar_expect_tx(bar_full(s), A_TILE_BYTES + C::B_TILE_BYTES);
+                    mbar_expect_tx(bar_full(s), A_TILE_BYTES + (g.b_presplit ? 2u : 1u) * C::B_TILE_BYTES);
                     const int k0 = (int)(kb * BK);
                     if (A_MN) {
 #pragma unroll
@@ -258,6 +295,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                         for (int j = 0; j < BN / 32; ++j) tma_load_2d(b_hi(s) + j * 4096, &mapB, bar_full(s), n0 + 32 * j, k0);
                     } else {
                         tma_load_2d(b_hi(s), &mapB, bar_full(s), k0, n0);
+                    }
+                    if (g.b_presplit) {
+                        if (B_MN) {
+#pragma unroll
+                            for (int j = 0; j < BN / 32; ++j) tma_load_2d(b_lo(s) + j * 4096, &mapBlo, bar_full(s), n0 + 32 * j, k0);
+                        } else {
+                            tma_load_2d(b_lo(s), &mapBlo, bar_full(s), k0, n0);
+                        }
                     }
                     if (++s == C::STAGES) { s = 0; ph ^= 1u; }
                 }
@@ -317,25 +362,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 mbar_wait(bar_full(s), ph);
                 float4 *hi = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES);
                 float4 *lo = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + A_TILE_BYTES);
-                auto split4 = [](float4 *ph4, float4 *pl4) {
+                const bool trunc = g.split_mode != 0;
+                auto split4 = [trunc](float4 *ph4, float4 *pl4) {
                     float4 x = *ph4, h, l;
-                    uint32_t u;
-#define MGGCN_SPLIT(c)                                                                   \
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.c));                                \
-    h.c = __uint_as_float(u);                                                            \
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x.c - h.c));                          \
-    l.c = __uint_as_float(u);
-                    MGGCN_SPLIT(x) MGGCN_SPLIT(y) MGGCN_SPLIT(z) MGGCN_SPLIT(w)
-#undef MGGCN_SPLIT
+                    split_tf32(x.x, h.x, l.x, trunc);
+                    split_tf32(x.y, h.y, l.y, trunc);
+                    split_tf32(x.z, h.z, l.z, trunc);
+                    split_tf32(x.w, h.w, l.w, trunc);
                     *ph4 = h;
                     *pl4 = l;
                 };
 #pragma unroll
                 for (int i = 0; i < (int)(A_TILE_BYTES / 16 / 128); ++i) split4(hi + tid + 128 * i, lo + tid + 128 * i);
-                float4 *bhi = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES);
-                float4 *blo = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES + C::B_TILE_BYTES);
+                if (!g.b_presplit) {
+                    float4 *bhi = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES);
+                    float4 *blo = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES + C::B_TILE_BYTES);
 #pragma unroll
-                for (int i = 0; i < (int)(C::B_TILE_BYTES / 16 / 128); ++i) split4(bhi + tid + 128 * i, blo + tid + 128 * i);
+                    for (int i = 0; i < (int)(C::B_TILE_BYTES / 16 / 128); ++i) split4(bhi + tid + 128 * i, blo + tid + 128 * i);
+                }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> tensor-core reads
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_conv(s));
@@ -537,7 +581,7 @@ split_plan plan_split(int ta, int64_t M, int64_t N, int64_t K, int bn) {
 }
 
 template <int BN, bool A_MN, bool B_MN>
-int launch(cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const tc_args &g) {
+int launch(cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &mbl, const tc_args &g) {
     using C = cfg<BN>;
     // the attribute is per device: one process may drive several GPUs (the mg_gcn CLI does)
     static std::atomic<bool> attr_set[64];
@@ -550,7 +594,7 @@ int launch(cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const 
     }
     const int64_t total = (int64_t)g.mt * g.nt * g.nz;
     const unsigned grid = (unsigned)std::min<int64_t>(total, g_sm_count);
-    gemm_tc_kernel<BN, A_MN, B_MN><<<grid, NTHREADS, C::SMEM_BYTES, st>>>(ma, mb, g);
+    gemm_tc_kernel<BN, A_MN, B_MN><<<grid, NTHREADS, C::SMEM_BYTES, st>>>(ma, mb, mbl, g);
     MGGCN_LAUNCH_CHECK();
     return MGGCN_OK;
 }
@@ -571,10 +615,21 @@ bool gemm_tc_eligible(int64_t M, int64_t N, int64_t K, const float *A, int64_t l
     return true;
 }
 
-size_t gemm_tc_workspace_bytes(int ta, int64_t M, int64_t N, int64_t K) {
+// The weight operand is pre-split when the product is tall (its cost is amortised over many row tiles) and B is small
+bool presplit_wanted(int ta, int64_t M, int64_t N, int64_t K) {
+    return g_gemm_presplit && !ta && M >= 4096 && K * ((N + 3) / 4 * 4) <= (1ll << 21) && N * ((K + 3) / 4 * 4) <= (1ll << 21);
+}
+size_t presplit_bytes(int tb, int64_t N, int64_t K) {
+    const int64_t rows = tb ? N : K, cols = tb ? K : N;
+    return (size_t)(2 * rows * ((cols + 3) / 4 * 4)) * sizeof(float) + 256;
+}
+
+size_t gemm_tc_workspace_bytes(int ta, int tb, int64_t M, int64_t N, int64_t K) {
     std::call_once(g_once, tc_init);
     const split_plan p = plan_split(ta, M, N, K, N <= 64 ? 64 : 128);
-    return p.nz > 1 ? (size_t)p.nz * (size_t)M * (size_t)N * sizeof(float) : 0;
+    size_t need = p.nz > 1 ? (size_t)p.nz * (size_t)M * (size_t)N * sizeof(float) : 0;
+    if (presplit_wanted(ta, M, N, K)) need = (need + 255) / 256 * 256 + presplit_bytes(tb, N, K);
+    return need;
 }
 
 int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, float alpha, const float *A, int64_t lda,
@@ -586,13 +641,33 @@ int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, fl
         sp.nz = 1;
         sp.kchunk = (K + BK - 1) / BK * BK;
     }
-    CUtensorMap ma, mb;
+    // pre-split weight operand: hi / lo arrays behind the split-K partials (never both in practice)
+    const size_t part_bytes = sp.nz > 1 ? ((size_t)sp.nz * M * N * sizeof(float) + 255) / 256 * 256 : 0;
+    const float *Bhi = B, *Blo = B;
+    int64_t ldbs = ldb;
+    const bool presplit = presplit_wanted(ta, M, N, K) && ws && ws_bytes >= part_bytes + presplit_bytes(tb, N, K);
+    if (presplit) {
+        const int64_t rows = tb ? N : K, cols = tb ? K : N;
+        ldbs = (cols + 3) / 4 * 4;
+        char *w = static_cast<char *>(ws) + part_bytes;
+        w += (256 - (reinterpret_cast<uintptr_t>(w) & 255)) & 255;
+        float *hi = reinterpret_cast<float *>(w), *lo = hi + rows * ldbs;
+        const int64_t total = rows * ldbs;
+        presplit_kernel<<<(unsigned)std::min<int64_t>((total + 255) / 256, 1024), 256, 0, st>>>(B, ldb, rows, cols, hi, lo, ldbs,
+                                                                                             g_gemm_split);
+        MGGCN_LAUNCH_CHECK();
+        Bhi = hi;
+        Blo = lo;
+    }
+    CUtensorMap ma, mb, mbl;
     // A: ta -> stored K x M (inner = M), boxes of 32 m x 32 k; else stored M x K (inner = K), box 32 k x 128 m
     if (ta) { int rc = make_map(&ma, A, M, K, lda, 32, BK, true); if (rc) return rc; }
     else { int rc = make_map(&ma, A, K, M, lda, BK, BM, false); if (rc) return rc; }
     // B: tb -> stored N x K (inner = K), box 32 k x BN n; else stored K x N (inner = N), boxes of 32 n x 32 k
-    if (tb) { int rc = make_map(&mb, B, K, N, ldb, BK, (uint32_t)bn, false); if (rc) return rc; }
-    else { int rc = make_map(&mb, B, N, K, ldb, 32, BK, true); if (rc) return rc; }
+    if (tb) { int rc = make_map(&mb, Bhi, K, N, ldbs, BK, (uint32_t)bn, false); if (rc) return rc; }
+    else { int rc = make_map(&mb, Bhi, N, K, ldbs, 32, BK, true); if (rc) return rc; }
+    if (tb) { int rc = make_map(&mbl, Blo, K, N, ldbs, BK, (uint32_t)bn, false); if (rc) return rc; }
+    else { int rc = make_map(&mbl, Blo, N, K, ldbs, 32, BK, true); if (rc) return rc; }
     tc_args g{};
     g.M = M; g.N = N; g.K = K;
     g.C = C; g.ldc = ldc;
@@ -602,19 +677,21 @@ int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, fl
     g.mt = (int)((M + BM - 1) / BM);
     g.nt = (int)((N + bn - 1) / bn);
     g.kgroup = std::max(1, g_gemm_kgroup);
+    g.split_mode = g_gemm_split;
+    g.b_presplit = presplit ? 1 : 0;
     g.alpha = alpha; g.beta = beta;
     g.epi = epi;
     int rc;
     if (bn == 64) {
-        if (ta && !tb) rc = launch<64, true, true>(st, ma, mb, g);
-        else if (ta && tb) rc = launch<64, true, false>(st, ma, mb, g);
-        else if (!ta && tb) rc = launch<64, false, false>(st, ma, mb, g);
-        else rc = launch<64, false, true>(st, ma, mb, g);
+        if (ta && !tb) rc = launch<64, true, true>(st, ma, mb, mbl, g);
+        else if (ta && tb) rc = launch<64, true, false>(st, ma, mb, mbl, g);
+        else if (!ta && tb) rc = launch<64, false, false>(st, ma, mb, mbl, g);
+        else rc = launch<64, false, true>(st, ma, mb, mbl, g);
     } else {
-        if (ta && !tb) rc = launch<128, true, true>(st, ma, mb, g);
-        else if (ta && tb) rc = launch<128, true, false>(st, ma, mb, g);
-        else if (!ta && tb) rc = launch<128, false, false>(st, ma, mb, g);
-        else rc = launch<128, false, true>(st, ma, mb, g);
+        if (ta && !tb) rc = launch<128, true, true>(st, ma, mb, mbl, g);
+        else if (ta && tb) rc = launch<128, true, false>(st, ma, mb, mbl, g);
+        else if (!ta && tb) rc = launch<128, false, false>(st, ma, mb, mbl, g);
+        else rc = launch<128, false, true>(st, ma, mb, mbl, g);
     }
     if (rc) return rc;
     if (sp.nz > 1) return launch_splitk_reduce(st, g.part, sp.nz, M, N, C, ldc, alpha, beta, epi);

@@ -15,6 +15,15 @@ sys.path.insert(0, ROOT)
 from __graft_entry__ import load_package  # noqa: E402
 
 
+def skewed_cuts(cuts, skew):
+    """Inner cuts moved by `skew` rows, odd ones up and even ones down: uneven row blocks."""
+    cuts = np.asarray(cuts).astype(np.int64)
+    for i in range(1, len(cuts) - 1):
+        cuts[i] += skew * (1 if i % 2 else -1)
+    assert np.all(np.diff(cuts) > 0)
+    return cuts.astype(np.uint32)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--comm", default="p2p")
@@ -46,9 +55,7 @@ def main():
             idt.copy_(torch.frombuffer(bytearray(bytes(buf)), dtype=torch.uint8))
         dist.broadcast(idt, 0)
         nccl_id = bytes(idt.cpu().numpy().tobytes())
-    cuts = mg.row_cuts(N, world)
-    for i in range(1, world):
-        cuts[i] += args.skew * (1 if i % 2 else -1)
+    cuts = skewed_cuts(mg.row_cuts(N, world), args.skew)
     if args.sharded:
         r0, r1 = int(cuts[rank]), int(cuts[rank + 1])
         slab, _, _, _ = mg.generate_rows("oracle4k", r0, r1, seed=1)

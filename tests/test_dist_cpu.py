@@ -86,3 +86,18 @@ def test_two_rank_host_path():
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(0, "ok"), (1, "ok")], res
+
+
+def test_checker_skewed_cuts_for_every_world_size(mg):
+    """The GPU checker's uneven cuts (tests/dist_engine_check.py --skew): even cuts move DOWN, which a uint32 array
+    refuses in place (the 8-GPU run of round 2 died there, not in the engine)."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("dist_engine_check", os.path.join(os.path.dirname(__file__), "dist_engine_check.py"))
+    chk = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(chk)
+    for world in (2, 4, 8):
+        cuts = chk.skewed_cuts(mg.row_cuts(4096, world), 11)
+        assert cuts.dtype == np.uint32 and cuts[0] == 0 and cuts[-1] == 4096
+        sizes = np.diff(cuts.astype(np.int64))
+        assert sizes.min() > 0 and (world == 2 or len(set(sizes.tolist())) > 1)
