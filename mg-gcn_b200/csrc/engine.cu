@@ -40,6 +40,9 @@ int g_xstreams = 2;
 int g_xpull = 0;
 // > 0: set_inputs reads pinned host rows with that many CTAs of pull_copy_kernel instead of a copy-engine transfer
 int g_h2d_sm = 0;
+// grouping of the stages of the grouped exchange: 0 = by the shape (see choose_groups), 1 = one launch per stage,
+// 2 = own | 1 | 2-3 | 4-7 | ...
+int g_xgroups = 0;
 void spmm_touched_cols_hint(int64_t n);
 int spmm_gathered(cudaStream_t st, int64_t rows, int64_t cols, const uint32_t *rowptr, const uint32_t *colidx,
                   const float *vals, float *gathered, int64_t ld, float *C, int64_t ldc, int F, float alpha,
@@ -315,6 +318,7 @@ struct mggcn_engine {
     // stages 2-3 | 4-7 | 8-15 -- each ordered behind the transfer of its last block with a stream event
     bool grouped = false;
     std::vector<std::pair<int, int>> groups;  // [first stage, end stage) per launch
+    bool groups_chosen = false;               // fixed by the first adjacency operand (choose_groups)
     float *gather = nullptr;
     uint32_t *stage_flags = nullptr;
     cudaEvent_t ev_bar = nullptr, ev_copied = nullptr;
@@ -830,7 +834,7 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
         for (int l = 0; l < cfg->num_layers; ++l) w = std::max<int64_t>(w, up4(std::min(cfg->sizes[l], cfg->sizes[l + 1])));
         if ((double)cfg->n_global * (double)w * 4.0 > 32.0 * (1ull << 30)) e->grouped = false;
     }
-    if (e->grouped) {
+    if (e->grouped) {  // provisional; choose_groups() decides once the block row is known
         e->groups.push_back({0, 1});
         for (int s0 = 1; s0 < e->P; s0 *= 2) e->groups.push_back({s0, std::min(2 * s0, e->P)});
     }
@@ -1041,6 +1045,43 @@ static int validate_csr(int64_t rows, int64_t cols, const uint64_t *rp, const ui
     return bad;
 }
 
+// Which stages share a launch in the grouped exchange.  Long groups give the kernel longer rows and grids (what an
+// 8 x 8 block lacks), but a group starts only when its LAST block has landed: the final group of the doubling
+// scheme holds half of the block row behind the whole exchange.  That is free while a block multiplies slower
+// than it travels (reddit-, proteins-shape: 60-75 entries per row and block) and costs up to half an aggregation
+// when the exchange is the longer side (products-shape at 8 GPUs: 6 entries per row and block, 313 MB blocks
+// that miss the L2: 12.4 of 30.3 ms exposed with the doubling scheme).  Estimate both sides per block:
+//   transfer = rows_blk * w * 4 / X,  multiply = nnz_blk * w * 4 / R
+// with X = 500 GB/s (what a rank receives while every rank pulls and multiplies) and R = the gather rate the SpMM
+// sustains (16 TB/s out of the L2, 6.5 TB/s when a block of B is larger than half the L2), i.e. the exchange is
+// the longer side when the entries per row and block are fewer than R / X.
+static void choose_groups(mggcn_engine *e, const uint64_t *const *blk_rowptr) {
+    if (!e->grouped || e->groups_chosen) return;
+    e->groups_chosen = true;
+    bool singles = g_xgroups == 1;
+    if (g_xgroups == 0) {
+        double nnz = 0;
+        for (int j = 0; j < e->P; ++j) nnz += (double)blk_rowptr[j][e->n];
+        const double per_row_and_block = nnz / std::max<double>(1.0, (double)e->n * (double)e->P);
+        int dev = 0, l2 = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, dev) != cudaSuccess || l2 <= 0) {
+            cudaGetLastError();
+            l2 = 126 << 20;
+        }
+        int64_t blk_rows = 0;
+        for (int j = 0; j < e->P; ++j) blk_rows = std::max<int64_t>(blk_rows, (int64_t)e->cuts[j + 1] - (int64_t)e->cuts[j]);
+        const double blk_bytes = (double)blk_rows * (double)e->maxw * 4.0;
+        const double R = blk_bytes > 0.5 * (double)l2 ? 6.5e12 : 16e12, X = 5e11;
+        singles = per_row_and_block < R / X;
+    }
+    e->groups.clear();
+    e->groups.push_back({0, 1});
+    if (singles)
+        for (int s0 = 1; s0 < e->P; ++s0) e->groups.push_back({s0, s0 + 1});
+    else
+        for (int s0 = 1; s0 < e->P; s0 *= 2) e->groups.push_back({s0, std::min(2 * s0, e->P)});
+}
+
 int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *const *blk_rowptr,
                                const uint32_t *const *blk_colidx, const float *const *blk_vals) {
     if (!e || which < 0 || which > 1 || !blk_rowptr || !blk_colidx || !blk_vals) return fail(MGGCN_E_INVALID, "bad argument");
@@ -1053,6 +1094,7 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
         if (rc) return fail(MGGCN_E_FORMAT, "adjacency block (%d, %d) is malformed: %s", e->rank, j,
                             rc == 1 ? "row pointers do not start at 0" : rc == 2 ? "row pointers decrease" : "column index out of range");
     }
+    choose_groups(e, blk_rowptr);
     size_t ws = e->ws_spmm_bytes;
     // merged CSRs over ranges of stages (global column ids into the all-gather buffer, every row in stage order:
     // blocks rank+s0, rank+s0+1, ... cyclically).  Gathered form: slot 0 = all remote stages [1, P) in one CSR, so

@@ -33,7 +33,7 @@ using namespace mggcn;
 namespace mggcn {
 extern int g_gemm_tc, g_gemm_kgroup, g_gemm_split, g_gemm_presplit;  // gemm_tc.cu
 extern int g_skip_exchange;           // engine.cu
-extern int g_xstreams, g_xpull, g_h2d_sm;  // engine.cu
+extern int g_xstreams, g_xpull, g_h2d_sm, g_xgroups;  // engine.cu
 }
 
 namespace {
@@ -1080,6 +1080,7 @@ int mggcn_tune(const char *key, int value) {
     else if (!strcmp(key, "skip_exchange")) slot = &mggcn::g_skip_exchange;
     else if (!strcmp(key, "xstreams")) slot = &mggcn::g_xstreams;
     else if (!strcmp(key, "xpull")) slot = &mggcn::g_xpull;
+    else if (!strcmp(key, "xgroups")) slot = &mggcn::g_xgroups;
     else if (!strcmp(key, "h2d_sm")) slot = &mggcn::g_h2d_sm;
     if (!slot) return fail(MGGCN_E_INVALID, "unknown tuning key %s", key);
     const int old = *slot;

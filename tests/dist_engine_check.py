@@ -33,12 +33,16 @@ def main():
     ap.add_argument("--hidden", type=int, nargs="+", default=[64, 64])
     ap.add_argument("--skew", type=int, default=0, help="move every inner cut by this many rows: uneven row blocks "
                                                         "(the reference's dense side needs N % P == 0, SURVEY D7; the engine does not)")
+    ap.add_argument("--xgroups", type=int, default=2, help="grouped exchange: 2 = own | 1 | 2-3 | 4-7 (the default here, so "
+                                                           "the long launches are exercised on a small graph), 1 = one launch "
+                                                           "per stage, 0 = the engine's own choice")
     ap.add_argument("--sharded", action="store_true", help="bench.py's pre-processing: every rank builds only its slab")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     mg = load_package()
+    mg.check(mg.lib().mggcn_tune(b"xgroups", args.xgroups))
     from oracle import oracle as orc
     A, X, Y, C = mg.generate("oracle4k", seed=1)
     N = A.n

@@ -202,6 +202,7 @@ def test_four_gpu_grouped_exchange_matches_oracle(cuda, graph):
 
 @pytest.mark.parametrize("comm,extra", [("p2p-grouped", []), ("p2p-grouped", ["--graph"]), ("p2p-staged", ["--graph"]),
                                         ("p2p-grouped", ["--no-overlap"]), ("p2p-grouped", ["--skew", "11"]),
+                                        ("p2p-grouped", ["--graph", "--xgroups", "1"]), ("p2p-grouped", ["--xgroups", "0"]),
                                         ("nccl", []), ("p2p", ["--graph"])])
 def test_eight_gpu_engine_matches_oracle(cuda, comm, extra):
     """World 8 -- the headline configuration.  Only here does the grouped exchange multiply stages 4-7 in ONE launch

@@ -42,6 +42,8 @@ def main():
     ap.add_argument("--n", type=int, default=232968)
     ap.add_argument("--kgroup", type=int, nargs="*", default=[2])
     ap.add_argument("--cublas", action="store_true")
+    ap.add_argument("--presplit", type=int, nargs="*", default=[1], help="weight operand split once per call (1) or per tile (0)")
+    ap.add_argument("--split", type=int, nargs="*", default=[0], help="0: both halves rounded to TF32; 1: truncated hi, exact lo")
     args = ap.parse_args()
     mg = load_package()
     L = mg.lib()
@@ -66,8 +68,11 @@ def main():
         scale = (opA[rows].abs().double() @ opB.abs().double()).amax(1, keepdim=True)
         flops = 2.0 * M * N * K
         byts = 4.0 * (M * K + K * N + M * N)
-        for tag, tc, kg in [("simt", 0, 0)] + [("tcgen05-3xtf32", 1, k) for k in args.kgroup]:
+        for tag, tc, kg, ps, sm in [("simt", 0, 0, 1, 0)] + [("tcgen05-3xtf32", 1, k, ps, sm) for k in args.kgroup
+                                                            for ps in args.presplit for sm in args.split]:
             L.mggcn_tune(b"gemm_tc", tc)
+            L.mggcn_tune(b"gemm_presplit", ps)
+            L.mggcn_tune(b"gemm_split", sm)
             if kg:
                 L.mggcn_tune(b"gemm_kgroup", kg)
             Cfull.zero_()
@@ -75,7 +80,7 @@ def main():
             torch.cuda.synchronize()
             err = float(((Cm[rows].double() - ref).abs() / scale.clamp_min(1e-30)).max())
             ms = timeit(lambda: mg.gemm(A, B, Cm, ta=bool(ta), tb=bool(tb)))
-            print(json.dumps({"tag": tag, "ta": ta, "tb": tb, "M": M, "N": N, "K": K, "kgroup": kg, "ms": round(ms, 4),
+            print(json.dumps({"tag": tag, "ta": ta, "tb": tb, "M": M, "N": N, "K": K, "kgroup": kg, "presplit": ps, "split": sm, "ms": round(ms, 4),
                               "TFLOPs": round(flops / ms / 1e9, 2), "GBps": round(byts / ms / 1e6, 1),
                               "max_rel_err": err}), flush=True)
         if args.cublas:
@@ -83,6 +88,8 @@ def main():
             print(json.dumps({"tag": "cublas-sgemm(torch)", "ta": ta, "tb": tb, "M": M, "N": N, "K": K, "ms": round(ms, 4),
                               "TFLOPs": round(flops / ms / 1e9, 2)}), flush=True)
     L.mggcn_tune(b"gemm_tc", 1)
+    L.mggcn_tune(b"gemm_presplit", 1)
+    L.mggcn_tune(b"gemm_split", 0)
 
 
 if __name__ == "__main__":
