@@ -41,6 +41,9 @@ int g_gemm_split = 0;    // 0: hi = rna_tf32(x), lo = rna_tf32(x - hi);  1: hi =
                          //    lo = x - hi left as it is (the tensor core drops its low bits): a third of the ALU work
 int g_gemm_presplit = 1; // a small B operand (the weights of H*W and G*W^T) is split once per call into hi / lo arrays
                          //    in the workspace and both halves arrive by TMA: the splitter warps only handle A
+int g_gemm_prefetch = 8; // k-blocks the TMA producer runs an L2 prefetch ahead of its loads (0 = none): the smem ring holds
+                         //    3-4 k-blocks, i.e. 16 KB of HBM-sourced bytes per stage -- too little in flight per SM to cover
+                         //    DRAM latency (measured 2.5-2.9 TB/s); prefetched tiles turn the ring's loads into L2 hits
 }  // namespace mggcn
 
 namespace {
@@ -75,6 +78,8 @@ struct tc_args {
     int kgroup;
     int split_mode;    // g_gemm_split
     int b_presplit;    // B's hi / lo come from mapB / mapBlo, nothing to split
+    int prefetch;      // k-blocks of L2 prefetch ahead of the loads
+    int prefetch_b;    // B streams from HBM too (X^T G): prefetch it as well
     float alpha, beta;
     mggcn_epilogue epi;
 };
@@ -121,6 +126,11 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *map, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1)
+                 : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -275,12 +285,51 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         if (lane == 0) {
             int s = 0;
             uint32_t ph = 0;
+            // L2 prefetch cursor: walks the same (tile, k-block) sequence g.prefetch steps ahead of the loads
+            int64_t pt = blockIdx.x, pkb = 0, pkb1 = 0;
+            int pm0 = 0, pn0 = 0, ahead = 0;
+            auto p_tile = [&]() {
+                if (pt >= total) return;
+                const int z = (int)(pt / tiles_mn);
+                const int64_t mn = pt - (int64_t)z * tiles_mn;
+                pm0 = (int)(mn % g.mt) * BM;
+                pn0 = (int)(mn / g.mt) * BN;
+                pkb = z * kb_per_z;
+                pkb1 = min(kb_all, pkb + kb_per_z);
+            };
+            auto p_step = [&]() {  // prefetch one k-block of the cursor's tile and advance
+                if (pt >= total) return;
+                const int k0 = (int)(pkb * BK);
+                if (A_MN) {
+#pragma unroll
+                    for (int j = 0; j < BM / 32; ++j) tma_prefetch_2d(&mapA, pm0 + 32 * j, k0);
+                } else {
+                    tma_prefetch_2d(&mapA, k0, pm0);
+                }
+                if (g.prefetch_b) {
+                    if (B_MN) {
+#pragma unroll
+                        for (int j = 0; j < BN / 32; ++j) tma_prefetch_2d(&mapB, pn0 + 32 * j, k0);
+                    } else {
+                        tma_prefetch_2d(&mapB, k0, pn0);
+                    }
+                }
+                if (++pkb >= pkb1) {
+                    pt += gridDim.x;
+                    p_tile();
+                }
+            };
+            if (g.prefetch > 0) {
+                p_tile();
+                for (; ahead < g.prefetch; ++ahead) p_step();
+            }
             for (int64_t t = blockIdx.x; t < total; t += gridDim.x) {
                 const int z = (int)(t / tiles_mn);
                 const int64_t mn = t - (int64_t)z * tiles_mn;
                 const int m0 = (int)(mn % g.mt) * BM, n0 = (int)(mn / g.mt) * BN;
                 const int64_t kb0 = z * kb_per_z, kb1 = min(kb_all, kb0 + kb_per_z);
                 for (int64_t kb = kb0; kb < kb1; ++kb) {
+                    if (g.prefetch > 0) p_step();
                     mbar_wait(bar_empty(s), ph ^ 1u);
                     mbar_expect_tx(bar_full(s), A_TILE_BYTES + (g.b_presplit ? 2u : 1u) * C::B_TILE_BYTES);
                     const int k0 = (int)(kb * BK);
@@ -679,6 +728,8 @@ int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, fl
     g.kgroup = std::max(1, g_gemm_kgroup);
     g.split_mode = g_gemm_split;
     g.b_presplit = presplit ? 1 : 0;
+    g.prefetch = std::max(0, std::min(g_gemm_prefetch, 64));
+    g.prefetch_b = !presplit && (double)N * (double)K * 4.0 > 8e6 ? 1 : 0;  // a B beyond a few MB is a streamed operand
     g.alpha = alpha; g.beta = beta;
     g.epi = epi;
     int rc;

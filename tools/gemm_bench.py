@@ -42,6 +42,8 @@ def main():
     ap.add_argument("--n", type=int, default=232968)
     ap.add_argument("--kgroup", type=int, nargs="*", default=[2])
     ap.add_argument("--cublas", action="store_true")
+    ap.add_argument("--shapes", default="reddit", choices=["reddit", "products"])
+    ap.add_argument("--tune", nargs="*", default=[], help="key=value knobs passed to mggcn_tune")
     ap.add_argument("--presplit", type=int, nargs="*", default=[1], help="weight operand split once per call (1) or per tile (0)")
     ap.add_argument("--split", type=int, nargs="*", default=[0], help="0: both halves rounded to TF32; 1: truncated hi, exact lo")
     args = ap.parse_args()
@@ -50,8 +52,14 @@ def main():
     n = args.n
     torch.backends.cuda.matmul.allow_tf32 = False
     # (ta, tb, M, N, K): forward H*W, backward G*W^T, weight gradient X^T*G
+    for kv in args.tune:
+        k, v = kv.split("=")
+        L.mggcn_tune(k.encode(), int(v))
     shapes = [(0, 0, n, 128, 608), (0, 0, n, 128, 128), (0, 0, n, 41, 128), (0, 1, n, 128, 41), (0, 1, n, 128, 128),
               (1, 0, 608, 128, n), (1, 0, 128, 128, n), (1, 0, 128, 41, n)]
+    if args.shapes == "products":  # 104 -> 256 -> 256 -> 256 -> 47 (48 padded)
+        shapes = [(0, 0, n, 256, 104), (0, 0, n, 256, 256), (0, 0, n, 48, 256), (0, 1, n, 256, 48), (0, 1, n, 256, 256),
+                  (1, 0, 104, 256, n), (1, 0, 256, 256, n), (1, 0, 256, 48, n)]
     for ta, tb, M, N, K in shapes:
         g = torch.Generator(device="cuda").manual_seed(M + N + K)
         ldn = (N + 3) // 4 * 4
