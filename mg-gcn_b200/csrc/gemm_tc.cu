@@ -41,9 +41,10 @@ int g_gemm_split = 0;    // 0: hi = rna_tf32(x), lo = rna_tf32(x - hi);  1: hi =
                          //    lo = x - hi left as it is (the tensor core drops its low bits): a third of the ALU work
 int g_gemm_presplit = 1; // a small B operand (the weights of H*W and G*W^T) is split once per call into hi / lo arrays
                          //    in the workspace and both halves arrive by TMA: the splitter warps only handle A
-int g_gemm_prefetch = 8; // k-blocks the TMA producer runs an L2 prefetch ahead of its loads (0 = none): the smem ring holds
-                         //    3-4 k-blocks, i.e. 16 KB of HBM-sourced bytes per stage -- too little in flight per SM to cover
-                         //    DRAM latency (measured 2.5-2.9 TB/s); prefetched tiles turn the ring's loads into L2 hits
+int g_gemm_ts = 1;       // A's hi / lo halves in tensor memory (TS form, see cfg); 0 = both operands in shared memory
+int g_gemm_prefetch = 0; // k-blocks the TMA producer runs an L2 prefetch ahead of its loads (0 = none).  Measured on the
+                         //    SS form: no gain at 4 / 8, -3..-8 % at 16 / 32 (profiles/r02_gemm_prefetch_sweep.txt) -- the ring
+                         //    was never waiting for DRAM, the shared-memory pipe was the limit
 }  // namespace mggcn
 
 namespace {
@@ -54,17 +55,28 @@ constexpr int UK = 8;            // tf32 UMMA K
 constexpr int NTHREADS = 448;
 constexpr int SPLIT_WARP0 = 2, EPI_WARP0 = 6;
 constexpr uint32_t A_TILE_BYTES = BM * BK * 4;  // 16 KB
-constexpr int STG_LD = 20;       // epilogue staging row stride (floats): 16-byte aligned rows, conflict-free float4 access
+constexpr int STG_LD = 16;       // epilogue staging row stride (floats); 16-byte chunk c of row r sits at chunk c ^ ((r >> 1) & 3):
+                                 // conflict-free for the row-per-lane writes and for the 8-rows-x-4-chunks reads
 
-template <int BN>
+// TS: A's hi / lo halves live in tensor memory (tcgen05.mma with a TMEM A operand), B's in shared memory.
+// The shared-memory data pipe is what bounds the all-smem (SS) form: ncu on the SS kernel shows the LSU side
+// (splitter loads / stores, epilogue staging) at 59 % and the tensor-core operand reads at 36 % of the pipe's peak,
+// 94 % together (profiles/r02_ncu_gemm_tc_n608.txt).  TS removes the hi / lo stores of A and half of the tensor
+// core's operand reads; per k-block the pipe moves 64 KB instead of 144 KB.
+template <int BN, bool TS>
 struct cfg {
-    static constexpr int STAGES = BN == 128 ? 3 : 4;
+    static constexpr int STAGES = TS ? (BN == 128 ? 4 : 6) : (BN == 128 ? 3 : 4);
     static constexpr uint32_t B_TILE_BYTES = BN * BK * 4;
-    static constexpr uint32_t STAGE_BYTES = 2 * A_TILE_BYTES + 2 * B_TILE_BYTES;
+    static constexpr uint32_t A_BYTES = (TS ? 1 : 2) * A_TILE_BYTES;  // raw tile only / hi + lo
+    static constexpr uint32_t STAGE_BYTES = A_BYTES + 2 * B_TILE_BYTES;
     static constexpr uint32_t STG_BYTES = 8 * 32 * STG_LD * 4;
     static constexpr uint32_t BAR_BYTES = 256;
     static constexpr uint32_t SMEM_BYTES = STAGES * STAGE_BYTES + STG_BYTES + BAR_BYTES + 1024;
-    static constexpr int TMEM_COLS = 2 * BN;  // two accumulator stages (power of two: 128 / 256)
+    static constexpr int A_COL0 = 2 * BN;                          // TS: first TMEM column of the A ring
+    static constexpr int A_COLS = 2 * BK;                          // TS: hi (32 columns) + lo (32 columns) per stage
+    static constexpr int TMEM_COLS = TS ? 512 : 2 * BN;            // accumulators (+ A ring): a power of two
+    static_assert(!TS || 2 * BN + STAGES * 2 * BK <= 512, "tensor memory has 512 columns");
+    static_assert(8 * (3 * STAGES + 4) + 4 <= (int)BAR_BYTES, "barrier table");
 };
 
 struct tc_args {
@@ -146,6 +158,26 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uin
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// 16 consecutive 32-bit columns of this thread's TMEM lane (32x32b: lane i of the warp <-> TMEM lane base + i)
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float *v) {
+    const uint32_t *r = reinterpret_cast<const uint32_t *>(v);
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+          "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float *v) {
     uint32_t *r = reinterpret_cast<uint32_t *>(v);
     asm volatile(
@@ -220,11 +252,11 @@ __device__ __forceinline__ float epi_apply(float x, const mggcn_epilogue &e, int
 // A_MN: A is stored K x M (m contiguous, the reference's A_T flag);  else M x K.
 // B_MN: B is stored K x N (n contiguous, the plain case);            else N x K (the B_T flag).
 // ---------------------------------------------------------------------------------------------
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool TS>
 __global__ void __launch_bounds__(NTHREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                const __grid_constant__ CUtensorMap mapBlo, const tc_args g) {
-    using C = cfg<BN>;
+    using C = cfg<BN, TS>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t *gen_base = smem_raw + (base - smem_u32(smem_raw));
@@ -239,10 +271,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     auto bar_tempty = [&](int a) { return bars + 8u * (3 * C::STAGES + 2 + a); };
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(gen_base + C::STAGES * C::STAGE_BYTES +
                                                                          C::STG_BYTES + 8 * (3 * C::STAGES + 4));
+    // stage layout: SS = [A hi (raw, split in place) | A lo | B hi | B lo];  TS = [A raw | B hi | B lo]
     auto a_hi = [&](int s) { return base + s * C::STAGE_BYTES; };
-    auto a_lo = [&](int s) { return base + s * C::STAGE_BYTES + A_TILE_BYTES; };
-    auto b_hi = [&](int s) { return base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES; };
-    auto b_lo = [&](int s) { return base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES + C::B_TILE_BYTES; };
+    auto a_lo = [&](int s) { return base + s * C::STAGE_BYTES + A_TILE_BYTES; };  // SS only
+    auto b_hi = [&](int s) { return base + s * C::STAGE_BYTES + C::A_BYTES; };
+    auto b_lo = [&](int s) { return base + s * C::STAGE_BYTES + C::A_BYTES + C::B_TILE_BYTES; };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -362,7 +395,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         if (lane == 0) {
             // instruction descriptor (cute::UMMA::InstrDescriptor): D=f32 [4,6), A=tf32 [7,10), B=tf32 [10,13),
             // a_major [15], b_major [16], N>>3 [17,23), M>>4 [24,29)
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+            // (a TMEM A operand is always K-major: lane = row, column = k)
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN && !TS ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                                    ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
             // K-major (SWIZZLE_128B): 8-row groups 1024 B apart (SBO), k step = 32 B inside the swizzle row.
             // MN-major (SWIZZLE_128B_BASE32B, atom = 4 k-rows x 128 B): 32-column chunks 4096 B apart (LBO),
@@ -382,14 +416,26 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     for (int64_t kb = kg; kb < kge; ++kb) {
                         mbar_wait(bar_conv(s), ph);
                         tc_fence_after();
-                        const uint64_t ah = smem_desc(a_hi(s), A_LBO, A_SBO, A_LAY), al = smem_desc(a_lo(s), A_LBO, A_SBO, A_LAY);
                         const uint64_t bh = smem_desc(b_hi(s), B_LBO, B_SBO, B_LAY), bl = smem_desc(b_lo(s), B_LBO, B_SBO, B_LAY);
+                        if constexpr (TS) {
+                            // A: TMEM columns [A_COL0 + 64 s, +32) = hi, the next 32 = lo; a k step is 8 columns
+                            const uint32_t th = tmem_base + (uint32_t)(C::A_COL0 + s * C::A_COLS), tl = th + (uint32_t)BK;
 #pragma unroll
-                        for (int k = 0; k < BK / UK; ++k) {
-                            const uint64_t ao = (uint64_t)((k * A_STEP) >> 4), bo = (uint64_t)((k * B_STEP) >> 4);
-                            tc_mma_tf32(d_tmem, al + ao, bh + bo, idesc, (kb > kg || k > 0) ? 1u : 0u);
-                            tc_mma_tf32(d_tmem, ah + ao, bl + bo, idesc, 1u);
-                            tc_mma_tf32(d_tmem, ah + ao, bh + bo, idesc, 1u);
+                            for (int k = 0; k < BK / UK; ++k) {
+                                const uint64_t bo = (uint64_t)((k * B_STEP) >> 4);
+                                tc_mma_tf32_ts(d_tmem, tl + (uint32_t)(k * UK), bh + bo, idesc, (kb > kg || k > 0) ? 1u : 0u);
+                                tc_mma_tf32_ts(d_tmem, th + (uint32_t)(k * UK), bl + bo, idesc, 1u);
+                                tc_mma_tf32_ts(d_tmem, th + (uint32_t)(k * UK), bh + bo, idesc, 1u);
+                            }
+                        } else {
+                            const uint64_t ah = smem_desc(a_hi(s), A_LBO, A_SBO, A_LAY), al = smem_desc(a_lo(s), A_LBO, A_SBO, A_LAY);
+#pragma unroll
+                            for (int k = 0; k < BK / UK; ++k) {
+                                const uint64_t ao = (uint64_t)((k * A_STEP) >> 4), bo = (uint64_t)((k * B_STEP) >> 4);
+                                tc_mma_tf32(d_tmem, al + ao, bh + bo, idesc, (kb > kg || k > 0) ? 1u : 0u);
+                                tc_mma_tf32(d_tmem, ah + ao, bl + bo, idesc, 1u);
+                                tc_mma_tf32(d_tmem, ah + ao, bh + bo, idesc, 1u);
+                            }
                         }
                         tc_commit(bar_empty(s));  // smem stage may be refilled once these MMAs have read it
                         if (++s == C::STAGES) { s = 0; ph ^= 1u; }
@@ -409,8 +455,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             const int64_t kb0 = z * kb_per_z, kb1 = min(kb_all, kb0 + kb_per_z);
             for (int64_t kb = kb0; kb < kb1; ++kb) {
                 mbar_wait(bar_full(s), ph);
-                float4 *hi = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES);
-                float4 *lo = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + A_TILE_BYTES);
                 const bool trunc = g.split_mode != 0;
                 auto split4 = [trunc](float4 *ph4, float4 *pl4) {
                     float4 x = *ph4, h, l;
@@ -421,15 +465,49 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     *ph4 = h;
                     *pl4 = l;
                 };
+                if constexpr (TS) {
+                    // thread <-> tile row <-> TMEM lane (a warp reaches the lane quarter warp % 4): read the row's 32
+                    // raw values of this k-block from shared memory, write hi / lo into the stage's TMEM columns
+                    tc_fence_after();
+                    const int q = warp & 3, row = q * 32 + lane;
+                    const uint8_t *araw = gen_base + s * C::STAGE_BYTES;
+                    const uint32_t t_hi = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(C::A_COL0 + s * C::A_COLS);
 #pragma unroll
-                for (int i = 0; i < (int)(A_TILE_BYTES / 16 / 128); ++i) split4(hi + tid + 128 * i, lo + tid + 128 * i);
+                    for (int hf = 0; hf < 2; ++hf) {
+                        float x[16], h[16], l[16];
+                        if constexpr (!A_MN) {
+                            // K-major tile: row r = 128 bytes, 16-byte chunk c at position c ^ (r % 8) (TMA SWIZZLE_128B)
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const float4 v = *reinterpret_cast<const float4 *>(araw + row * 128 + (((hf * 4 + j) ^ (row & 7)) << 4));
+                                x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+                            }
+                        } else {
+                            // MN-major tile: four unswizzled boxes of 32 k-rows x 32 m; this warp's rows are box q
+#pragma unroll
+                            for (int k = 0; k < 16; ++k)
+                                x[k] = *reinterpret_cast<const float *>(araw + q * 4096 + (hf * 16 + k) * 128 + lane * 4);
+                        }
+#pragma unroll
+                        for (int k = 0; k < 16; ++k) split_tf32(x[k], h[k], l[k], trunc);
+                        tmem_st16(t_hi + (uint32_t)(hf * 16), h);
+                        tmem_st16(t_hi + (uint32_t)(BK + hf * 16), l);
+                    }
+                    tmem_st_wait();
+                } else {
+                    float4 *hi = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES);
+                    float4 *lo = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + A_TILE_BYTES);
+#pragma unroll
+                    for (int i = 0; i < (int)(A_TILE_BYTES / 16 / 128); ++i) split4(hi + tid + 128 * i, lo + tid + 128 * i);
+                }
                 if (!g.b_presplit) {
-                    float4 *bhi = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES);
-                    float4 *blo = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + 2 * A_TILE_BYTES + C::B_TILE_BYTES);
+                    float4 *bhi = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + C::A_BYTES);
+                    float4 *blo = reinterpret_cast<float4 *>(gen_base + s * C::STAGE_BYTES + C::A_BYTES + C::B_TILE_BYTES);
 #pragma unroll
                     for (int i = 0; i < (int)(C::B_TILE_BYTES / 16 / 128); ++i) split4(bhi + tid + 128 * i, blo + tid + 128 * i);
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> tensor-core reads
+                if constexpr (TS) tc_fence_before();                          // tcgen05.st -> the issuer's tcgen05.mma
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_conv(s));
                 if (++s == C::STAGES) { s = 0; ph ^= 1u; }
@@ -488,7 +566,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             for (int c = 0; c < CW / 16; ++c) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
-                    *reinterpret_cast<float4 *>(my_stg + lane * STG_LD + 4 * j) =
+                    *reinterpret_cast<float4 *>(my_stg + lane * STG_LD + 4 * (j ^ ((lane >> 1) & 3))) =
                         make_float4(acc[c * 16 + 4 * j], acc[c * 16 + 4 * j + 1], acc[c * 16 + 4 * j + 2], acc[c * 16 + 4 * j + 3]);
                 __syncwarp();
                 const int64_t col = n0 + c * 16 + c4;
@@ -514,7 +592,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     for (int i = 0; i < 4; ++i) {
                         const int64_t row = row0 + 8 * i;
                         if (row >= g.M) break;
-                        float4 x4 = *reinterpret_cast<const float4 *>(my_stg + (8 * i + r_in) * STG_LD + c4);
+                        float4 x4 = *reinterpret_cast<const float4 *>(my_stg + (8 * i + r_in) * STG_LD + (c4 ^ (((r_in >> 1) & 3) << 2)));
                         if (!split) {
                             float x[4] = {x4.x, x4.y, x4.z, x4.w};
                             const float o[4] = {old[i].x, old[i].y, old[i].z, old[i].w};
@@ -542,7 +620,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                         const int64_t row = row0 + 8 * i;
                         if (row >= g.M) break;
                         for (int e = 0; e < 4 && col + e < g.N; ++e) {
-                            float x = my_stg[(8 * i + r_in) * STG_LD + c4 + e];
+                            float x = my_stg[(8 * i + r_in) * STG_LD + (c4 ^ (((r_in >> 1) & 3) << 2)) + e];
                             float *cp = out + row * ldo + col + e;
                             if (!split) {
                                 x *= g.alpha;
@@ -596,14 +674,16 @@ void tc_init() {
 
 // 2-D fp32 tensor map over a row-major array: `inner` contiguous elements, `outer` rows of `ld` elements.
 // mn_major: the operand's M/N index is the contiguous one -> 32-byte-atom 128-byte swizzle (see smem_desc)
+// plain: no swizzle (a tile that only threads read: the MN-major A operand of the TS form)
 int make_map(CUtensorMap *m, const float *p, int64_t inner, int64_t outer, int64_t ld, uint32_t box_inner,
-             uint32_t box_outer, bool mn_major) {
+             uint32_t box_outer, bool mn_major, bool plain = false) {
     cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
     cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
     cuuint32_t box[2] = {box_inner, box_outer};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(p), dims, strides, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          plain ? CU_TENSOR_MAP_SWIZZLE_NONE : mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(MGGCN_E_INVALID, "cuTensorMapEncodeTiled failed (%d)", (int)r);
@@ -629,21 +709,21 @@ split_plan plan_split(int ta, int64_t M, int64_t N, int64_t K, int bn) {
     return p;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool TS>
 int launch(cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &mbl, const tc_args &g) {
-    using C = cfg<BN>;
+    using C = cfg<BN, TS>;
     // the attribute is per device: one process may drive several GPUs (the mg_gcn CLI does)
     static std::atomic<bool> attr_set[64];
     int dev = 0;
     MGGCN_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
-        MGGCN_CUDA_TRY(cudaFuncSetAttribute(gemm_tc_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        MGGCN_CUDA_TRY(cudaFuncSetAttribute(gemm_tc_kernel<BN, A_MN, B_MN, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)C::SMEM_BYTES));
         if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
     const int64_t total = (int64_t)g.mt * g.nt * g.nz;
     const unsigned grid = (unsigned)std::min<int64_t>(total, g_sm_count);
-    gemm_tc_kernel<BN, A_MN, B_MN><<<grid, NTHREADS, C::SMEM_BYTES, st>>>(ma, mb, mbl, g);
+    gemm_tc_kernel<BN, A_MN, B_MN, TS><<<grid, NTHREADS, C::SMEM_BYTES, st>>>(ma, mb, mbl, g);
     MGGCN_LAUNCH_CHECK();
     return MGGCN_OK;
 }
@@ -710,7 +790,8 @@ int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, fl
     }
     CUtensorMap ma, mb, mbl;
     // A: ta -> stored K x M (inner = M), boxes of 32 m x 32 k; else stored M x K (inner = K), box 32 k x 128 m
-    if (ta) { int rc = make_map(&ma, A, M, K, lda, 32, BK, true); if (rc) return rc; }
+    const bool ts = g_gemm_ts != 0;
+    if (ta) { int rc = make_map(&ma, A, M, K, lda, 32, BK, true, ts); if (rc) return rc; }
     else { int rc = make_map(&ma, A, K, M, lda, BK, BM, false); if (rc) return rc; }
     // B: tb -> stored N x K (inner = K), box 32 k x BN n; else stored K x N (inner = N), boxes of 32 n x 32 k
     if (tb) { int rc = make_map(&mb, Bhi, K, N, ldbs, BK, (uint32_t)bn, false); if (rc) return rc; }
@@ -733,17 +814,14 @@ int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, fl
     g.alpha = alpha; g.beta = beta;
     g.epi = epi;
     int rc;
-    if (bn == 64) {
-        if (ta && !tb) rc = launch<64, true, true>(st, ma, mb, mbl, g);
-        else if (ta && tb) rc = launch<64, true, false>(st, ma, mb, mbl, g);
-        else if (!ta && tb) rc = launch<64, false, false>(st, ma, mb, mbl, g);
-        else rc = launch<64, false, true>(st, ma, mb, mbl, g);
-    } else {
-        if (ta && !tb) rc = launch<128, true, true>(st, ma, mb, mbl, g);
-        else if (ta && tb) rc = launch<128, true, false>(st, ma, mb, mbl, g);
-        else if (!ta && tb) rc = launch<128, false, false>(st, ma, mb, mbl, g);
-        else rc = launch<128, false, true>(st, ma, mb, mbl, g);
-    }
+#define MGGCN_TC_LAUNCH(BN_, TS_)                                                            \
+    (ta && !tb   ? launch<BN_, true, true, TS_>(st, ma, mb, mbl, g)                           \
+     : ta && tb  ? launch<BN_, true, false, TS_>(st, ma, mb, mbl, g)                          \
+     : !ta && tb ? launch<BN_, false, false, TS_>(st, ma, mb, mbl, g)                         \
+                 : launch<BN_, false, true, TS_>(st, ma, mb, mbl, g))
+    if (bn == 64) rc = ts ? MGGCN_TC_LAUNCH(64, true) : MGGCN_TC_LAUNCH(64, false);
+    else rc = ts ? MGGCN_TC_LAUNCH(128, true) : MGGCN_TC_LAUNCH(128, false);
+#undef MGGCN_TC_LAUNCH
     if (rc) return rc;
     if (sp.nz > 1) return launch_splitk_reduce(st, g.part, sp.nz, M, N, C, ldc, alpha, beta, epi);
     return MGGCN_OK;
