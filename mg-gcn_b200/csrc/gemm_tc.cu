@@ -42,9 +42,6 @@ int g_gemm_split = 0;    // 0: hi = rna_tf32(x), lo = rna_tf32(x - hi);  1: hi =
 int g_gemm_presplit = 1; // a small B operand (the weights of H*W and G*W^T) is split once per call into hi / lo arrays
                          //    in the workspace and both halves arrive by TMA: the splitter warps only handle A
 int g_gemm_ts = 1;       // A's hi / lo halves in tensor memory (TS form, see cfg); 0 = both operands in shared memory
-int g_gemm_prefetch = 0; // k-blocks the TMA producer runs an L2 prefetch ahead of its loads (0 = none).  Measured on the
-                         //    SS form: no gain at 4 / 8, -3..-8 % at 16 / 32 (profiles/r02_gemm_prefetch_sweep.txt) -- the ring
-                         //    was never waiting for DRAM, the shared-memory pipe was the limit
 }  // namespace mggcn
 
 namespace {
@@ -89,9 +86,10 @@ struct tc_args {
     int mt, nt;        // tiles along M, N
     int kgroup;
     int split_mode;    // g_gemm_split
-    int b_presplit;    // B's hi / lo come from mapB / mapBlo, nothing to split
-    int prefetch;      // k-blocks of L2 prefetch ahead of the loads
-    int prefetch_b;    // B streams from HBM too (X^T G): prefetch it as well
+    int b_presplit;    // B's hi / lo halves sit behind each other in the workspace and arrive as one box of mapB
+    int a_one, b_one;  // an MN-major operand whose extent is a multiple of 32 arrives as ONE 3-D box per k-block
+                       // (chunk, k, 32 contiguous) instead of BM/32 (BN/32) 2-D boxes: the producer is one thread, and
+                       // nine cp.async.bulk.tensor per k-block kept it busy 80 % of the time (ncu source page, round 2)
     float alpha, beta;
     mggcn_epilogue epi;
 };
@@ -139,10 +137,17 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
         ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
-__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *map, int c0, int c1) {
-    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];"
-                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1)
-                 : "memory");
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -254,8 +259,7 @@ __device__ __forceinline__ float epi_apply(float x, const mggcn_epilogue &e, int
 // ---------------------------------------------------------------------------------------------
 template <int BN, bool A_MN, bool B_MN, bool TS>
 __global__ void __launch_bounds__(NTHREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
-               const __grid_constant__ CUtensorMap mapBlo, const tc_args g) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const tc_args g) {
     using C = cfg<BN, TS>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -282,7 +286,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
-        if (g.b_presplit) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapBlo)) : "memory");
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < C::STAGES; ++s) {
@@ -318,73 +321,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         if (lane == 0) {
             int s = 0;
             uint32_t ph = 0;
-            // L2 prefetch cursor: walks the same (tile, k-block) sequence g.prefetch steps ahead of the loads
-            int64_t pt = blockIdx.x, pkb = 0, pkb1 = 0;
-            int pm0 = 0, pn0 = 0, ahead = 0;
-            auto p_tile = [&]() {
-                if (pt >= total) return;
-                const int z = (int)(pt / tiles_mn);
-                const int64_t mn = pt - (int64_t)z * tiles_mn;
-                pm0 = (int)(mn % g.mt) * BM;
-                pn0 = (int)(mn / g.mt) * BN;
-                pkb = z * kb_per_z;
-                pkb1 = min(kb_all, pkb + kb_per_z);
-            };
-            auto p_step = [&]() {  // prefetch one k-block of the cursor's tile and advance
-                if (pt >= total) return;
-                const int k0 = (int)(pkb * BK);
-                if (A_MN) {
-#pragma unroll
-                    for (int j = 0; j < BM / 32; ++j) tma_prefetch_2d(&mapA, pm0 + 32 * j, k0);
-                } else {
-                    tma_prefetch_2d(&mapA, k0, pm0);
-                }
-                if (g.prefetch_b) {
-                    if (B_MN) {
-#pragma unroll
-                        for (int j = 0; j < BN / 32; ++j) tma_prefetch_2d(&mapB, pn0 + 32 * j, k0);
-                    } else {
-                        tma_prefetch_2d(&mapB, k0, pn0);
-                    }
-                }
-                if (++pkb >= pkb1) {
-                    pt += gridDim.x;
-                    p_tile();
-                }
-            };
-            if (g.prefetch > 0) {
-                p_tile();
-                for (; ahead < g.prefetch; ++ahead) p_step();
-            }
             for (int64_t t = blockIdx.x; t < total; t += gridDim.x) {
                 const int z = (int)(t / tiles_mn);
                 const int64_t mn = t - (int64_t)z * tiles_mn;
                 const int m0 = (int)(mn % g.mt) * BM, n0 = (int)(mn / g.mt) * BN;
                 const int64_t kb0 = z * kb_per_z, kb1 = min(kb_all, kb0 + kb_per_z);
                 for (int64_t kb = kb0; kb < kb1; ++kb) {
-                    if (g.prefetch > 0) p_step();
                     mbar_wait(bar_empty(s), ph ^ 1u);
                     mbar_expect_tx(bar_full(s), A_TILE_BYTES + (g.b_presplit ? 2u : 1u) * C::B_TILE_BYTES);
                     const int k0 = (int)(kb * BK);
                     if (A_MN) {
+                        if (g.a_one) {
+                            tma_load_3d(a_hi(s), &mapA, bar_full(s), 0, k0, m0 / 32);
+                        } else {
 #pragma unroll
-                        for (int j = 0; j < BM / 32; ++j) tma_load_2d(a_hi(s) + j * 4096, &mapA, bar_full(s), m0 + 32 * j, k0);
+                            for (int j = 0; j < BM / 32; ++j) tma_load_2d(a_hi(s) + j * 4096, &mapA, bar_full(s), m0 + 32 * j, k0);
+                        }
                     } else {
                         tma_load_2d(a_hi(s), &mapA, bar_full(s), k0, m0);
                     }
-                    if (B_MN) {
+                    if (g.b_presplit) {  // hi and lo in one box: [half][chunk][k][32 n] or [half][n][k]
+                        if (B_MN) tma_load_4d(b_hi(s), &mapB, bar_full(s), 0, k0, n0 / 32, 0);
+                        else tma_load_3d(b_hi(s), &mapB, bar_full(s), k0, n0, 0);
+                    } else if (B_MN) {
+                        if (g.b_one) {
+                            tma_load_3d(b_hi(s), &mapB, bar_full(s), 0, k0, n0 / 32);
+                        } else {
 #pragma unroll
-                        for (int j = 0; j < BN / 32; ++j) tma_load_2d(b_hi(s) + j * 4096, &mapB, bar_full(s), n0 + 32 * j, k0);
+                            for (int j = 0; j < BN / 32; ++j) tma_load_2d(b_hi(s) + j * 4096, &mapB, bar_full(s), n0 + 32 * j, k0);
+                        }
                     } else {
                         tma_load_2d(b_hi(s), &mapB, bar_full(s), k0, n0);
-                    }
-                    if (g.b_presplit) {
-                        if (B_MN) {
-#pragma unroll
-                            for (int j = 0; j < BN / 32; ++j) tma_load_2d(b_lo(s) + j * 4096, &mapBlo, bar_full(s), n0 + 32 * j, k0);
-                        } else {
-                            tma_load_2d(b_lo(s), &mapBlo, bar_full(s), k0, n0);
-                        }
                     }
                     if (++s == C::STAGES) { s = 0; ph ^= 1u; }
                 }
@@ -472,24 +439,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     const int q = warp & 3, row = q * 32 + lane;
                     const uint8_t *araw = gen_base + s * C::STAGE_BYTES;
                     const uint32_t t_hi = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(C::A_COL0 + s * C::A_COLS);
+                    float x[BK];
+                    if constexpr (!A_MN) {
+                        // K-major tile: row r = 128 bytes, 16-byte chunk c at position c ^ (r % 8) (TMA SWIZZLE_128B)
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 v = *reinterpret_cast<const float4 *>(araw + row * 128 + ((j ^ (row & 7)) << 4));
+                            x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+                        }
+                    } else {
+                        // MN-major tile: four unswizzled boxes of 32 k-rows x 32 m; this warp's rows are box q
+#pragma unroll
+                        for (int k = 0; k < BK; ++k) x[k] = *reinterpret_cast<const float *>(araw + q * 4096 + k * 128 + lane * 4);
+                    }
 #pragma unroll
                     for (int hf = 0; hf < 2; ++hf) {
-                        float x[16], h[16], l[16];
-                        if constexpr (!A_MN) {
-                            // K-major tile: row r = 128 bytes, 16-byte chunk c at position c ^ (r % 8) (TMA SWIZZLE_128B)
+                        float h[16], l[16];
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                const float4 v = *reinterpret_cast<const float4 *>(araw + row * 128 + (((hf * 4 + j) ^ (row & 7)) << 4));
-                                x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
-                            }
-                        } else {
-                            // MN-major tile: four unswizzled boxes of 32 k-rows x 32 m; this warp's rows are box q
-#pragma unroll
-                            for (int k = 0; k < 16; ++k)
-                                x[k] = *reinterpret_cast<const float *>(araw + q * 4096 + (hf * 16 + k) * 128 + lane * 4);
-                        }
-#pragma unroll
-                        for (int k = 0; k < 16; ++k) split_tf32(x[k], h[k], l[k], trunc);
+                        for (int k = 0; k < 16; ++k) split_tf32(x[hf * 16 + k], h[k], l[k], trunc);
                         tmem_st16(t_hi + (uint32_t)(hf * 16), h);
                         tmem_st16(t_hi + (uint32_t)(BK + hf * 16), l);
                     }
@@ -690,6 +657,19 @@ int make_map(CUtensorMap *m, const float *p, int64_t inner, int64_t outer, int64
     return MGGCN_OK;
 }
 
+// n-dimensional view (rank 3 or 4) for operands that arrive as one box per k-block; strides in elements
+int make_map_nd(CUtensorMap *m, const float *p, int rank, const int64_t *dims, const int64_t *strides, const uint32_t *box,
+                CUtensorMapSwizzle sw) {
+    cuuint64_t d[4], st[3];
+    cuuint32_t b[4], es[4] = {1, 1, 1, 1};
+    for (int i = 0; i < rank; ++i) { d[i] = (cuuint64_t)dims[i]; b[i] = box[i]; }
+    for (int i = 0; i + 1 < rank; ++i) st[i] = (cuuint64_t)strides[i] * 4;
+    CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<float *>(p), d, st, b, es,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(MGGCN_E_INVALID, "cuTensorMapEncodeTiled (rank %d) failed (%d)", rank, (int)r);
+    return MGGCN_OK;
+}
+
 struct split_plan {
     int nz;
     int64_t kchunk;
@@ -710,7 +690,7 @@ split_plan plan_split(int ta, int64_t M, int64_t N, int64_t K, int bn) {
 }
 
 template <int BN, bool A_MN, bool B_MN, bool TS>
-int launch(cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &mbl, const tc_args &g) {
+int launch(cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const tc_args &g) {
     using C = cfg<BN, TS>;
     // the attribute is per device: one process may drive several GPUs (the mg_gcn CLI does)
     static std::atomic<bool> attr_set[64];
@@ -723,7 +703,7 @@ int launch(cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const 
     }
     const int64_t total = (int64_t)g.mt * g.nt * g.nz;
     const unsigned grid = (unsigned)std::min<int64_t>(total, g_sm_count);
-    gemm_tc_kernel<BN, A_MN, B_MN, TS><<<grid, NTHREADS, C::SMEM_BYTES, st>>>(ma, mb, mbl, g);
+    gemm_tc_kernel<BN, A_MN, B_MN, TS><<<grid, NTHREADS, C::SMEM_BYTES, st>>>(ma, mb, g);
     MGGCN_LAUNCH_CHECK();
     return MGGCN_OK;
 }
@@ -746,11 +726,13 @@ bool gemm_tc_eligible(int64_t M, int64_t N, int64_t K, const float *A, int64_t l
 
 // The weight operand is pre-split when the product is tall (its cost is amortised over many row tiles) and B is small
 bool presplit_wanted(int ta, int64_t M, int64_t N, int64_t K) {
-    return g_gemm_presplit && !ta && M >= 4096 && K * ((N + 3) / 4 * 4) <= (1ll << 21) && N * ((K + 3) / 4 * 4) <= (1ll << 21);
+    return g_gemm_presplit && !ta && M >= 4096 && K * ((N + 31) / 32 * 32) <= (1ll << 21) && N * ((K + 3) / 4 * 4) <= (1ll << 21);
 }
+// pitch of the hi / lo copies: the MN-major form (K x N) is read in 32-column chunks, so its rows are padded to 32
+int64_t presplit_ld(int tb, int64_t N, int64_t K) { return tb ? (K + 3) / 4 * 4 : (N + 31) / 32 * 32; }
 size_t presplit_bytes(int tb, int64_t N, int64_t K) {
-    const int64_t rows = tb ? N : K, cols = tb ? K : N;
-    return (size_t)(2 * rows * ((cols + 3) / 4 * 4)) * sizeof(float) + 256;
+    const int64_t rows = tb ? N : K;
+    return (size_t)(2 * rows * presplit_ld(tb, N, K)) * sizeof(float) + 256;
 }
 
 size_t gemm_tc_workspace_bytes(int ta, int tb, int64_t M, int64_t N, int64_t K) {
@@ -772,32 +754,57 @@ int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, fl
     }
     // pre-split weight operand: hi / lo arrays behind the split-K partials (never both in practice)
     const size_t part_bytes = sp.nz > 1 ? ((size_t)sp.nz * M * N * sizeof(float) + 255) / 256 * 256 : 0;
-    const float *Bhi = B, *Blo = B;
+    const float *Bs = B;
     int64_t ldbs = ldb;
     const bool presplit = presplit_wanted(ta, M, N, K) && ws && ws_bytes >= part_bytes + presplit_bytes(tb, N, K);
+    const int64_t b_rows = tb ? N : K, b_cols = tb ? K : N;
     if (presplit) {
-        const int64_t rows = tb ? N : K, cols = tb ? K : N;
-        ldbs = (cols + 3) / 4 * 4;
+        ldbs = presplit_ld(tb, N, K);
         char *w = static_cast<char *>(ws) + part_bytes;
         w += (256 - (reinterpret_cast<uintptr_t>(w) & 255)) & 255;
-        float *hi = reinterpret_cast<float *>(w), *lo = hi + rows * ldbs;
-        const int64_t total = rows * ldbs;
-        presplit_kernel<<<(unsigned)std::min<int64_t>((total + 255) / 256, 1024), 256, 0, st>>>(B, ldb, rows, cols, hi, lo, ldbs,
+        float *hi = reinterpret_cast<float *>(w), *lo = hi + b_rows * ldbs;
+        const int64_t total = b_rows * ldbs;
+        presplit_kernel<<<(unsigned)std::min<int64_t>((total + 255) / 256, 1024), 256, 0, st>>>(B, ldb, b_rows, b_cols, hi, lo, ldbs,
                                                                                              g_gemm_split);
         MGGCN_LAUNCH_CHECK();
-        Bhi = hi;
-        Blo = lo;
+        Bs = hi;
     }
-    CUtensorMap ma, mb, mbl;
-    // A: ta -> stored K x M (inner = M), boxes of 32 m x 32 k; else stored M x K (inner = K), box 32 k x 128 m
+    CUtensorMap ma, mb;
     const bool ts = g_gemm_ts != 0;
-    if (ta) { int rc = make_map(&ma, A, M, K, lda, 32, BK, true, ts); if (rc) return rc; }
-    else { int rc = make_map(&ma, A, K, M, lda, BK, BM, false); if (rc) return rc; }
-    // B: tb -> stored N x K (inner = K), box 32 k x BN n; else stored K x N (inner = N), boxes of 32 n x 32 k
-    if (tb) { int rc = make_map(&mb, Bhi, K, N, ldbs, BK, (uint32_t)bn, false); if (rc) return rc; }
-    else { int rc = make_map(&mb, Bhi, N, K, ldbs, 32, BK, true); if (rc) return rc; }
-    if (tb) { int rc = make_map(&mbl, Blo, K, N, ldbs, BK, (uint32_t)bn, false); if (rc) return rc; }
-    else { int rc = make_map(&mbl, Blo, N, K, ldbs, 32, BK, true); if (rc) return rc; }
+    // A: ta -> stored K x M (inner = M): one 3-D box (32 m, 32 k, 4 chunks) when M is a multiple of 32, else four
+    // 2-D boxes of 32 m x 32 k; not ta -> stored M x K (inner = K), one box 32 k x 128 m
+    const bool a_one = ta && M % 32 == 0;
+    if (a_one) {
+        const int64_t dims[3] = {32, K, M / 32}, str[2] = {lda, 32};
+        const uint32_t box[3] = {32, (uint32_t)BK, (uint32_t)(BM / 32)};
+        int rc = make_map_nd(&ma, A, 3, dims, str, box, ts ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+        if (rc) return rc;
+    } else if (ta) {
+        int rc = make_map(&ma, A, M, K, lda, 32, BK, true, ts); if (rc) return rc;
+    } else {
+        int rc = make_map(&ma, A, K, M, lda, BK, BM, false); if (rc) return rc;
+    }
+    // B: tb -> stored N x K (inner = K), box 32 k x BN n; else stored K x N (inner = N), 32-column chunks.
+    // The pre-split copies add an outermost dimension of 2 (hi, lo) so that both halves are one box.
+    bool b_one = false;
+    if (presplit && tb) {
+        const int64_t dims[3] = {K, N, 2}, str[2] = {ldbs, b_rows * ldbs};
+        const uint32_t box[3] = {(uint32_t)BK, (uint32_t)bn, 2};
+        int rc = make_map_nd(&mb, Bs, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B); if (rc) return rc;
+    } else if (presplit) {
+        const int64_t dims[4] = {32, K, ldbs / 32, 2}, str[3] = {ldbs, 32, b_rows * ldbs};
+        const uint32_t box[4] = {32, (uint32_t)BK, (uint32_t)(bn / 32), 2};
+        int rc = make_map_nd(&mb, Bs, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B); if (rc) return rc;
+    } else if (tb) {
+        int rc = make_map(&mb, B, K, N, ldb, BK, (uint32_t)bn, false); if (rc) return rc;
+    } else if (N % 32 == 0) {
+        b_one = true;
+        const int64_t dims[3] = {32, K, N / 32}, str[2] = {ldb, 32};
+        const uint32_t box[3] = {32, (uint32_t)BK, (uint32_t)(bn / 32)};
+        int rc = make_map_nd(&mb, B, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B); if (rc) return rc;
+    } else {
+        int rc = make_map(&mb, B, N, K, ldb, 32, BK, true); if (rc) return rc;
+    }
     tc_args g{};
     g.M = M; g.N = N; g.K = K;
     g.C = C; g.ldc = ldc;
@@ -809,16 +816,16 @@ int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, fl
     g.kgroup = std::max(1, g_gemm_kgroup);
     g.split_mode = g_gemm_split;
     g.b_presplit = presplit ? 1 : 0;
-    g.prefetch = std::max(0, std::min(g_gemm_prefetch, 64));
-    g.prefetch_b = !presplit && (double)N * (double)K * 4.0 > 8e6 ? 1 : 0;  // a B beyond a few MB is a streamed operand
+    g.a_one = a_one ? 1 : 0;
+    g.b_one = b_one ? 1 : 0;
     g.alpha = alpha; g.beta = beta;
     g.epi = epi;
     int rc;
 #define MGGCN_TC_LAUNCH(BN_, TS_)                                                            \
-    (ta && !tb   ? launch<BN_, true, true, TS_>(st, ma, mb, mbl, g)                           \
-     : ta && tb  ? launch<BN_, true, false, TS_>(st, ma, mb, mbl, g)                          \
-     : !ta && tb ? launch<BN_, false, false, TS_>(st, ma, mb, mbl, g)                         \
-                 : launch<BN_, false, true, TS_>(st, ma, mb, mbl, g))
+    (ta && !tb   ? launch<BN_, true, true, TS_>(st, ma, mb, g)                           \
+     : ta && tb  ? launch<BN_, true, false, TS_>(st, ma, mb, g)                          \
+     : !ta && tb ? launch<BN_, false, false, TS_>(st, ma, mb, g)                         \
+                 : launch<BN_, false, true, TS_>(st, ma, mb, g))
     if (bn == 64) rc = ts ? MGGCN_TC_LAUNCH(64, true) : MGGCN_TC_LAUNCH(64, false);
     else rc = ts ? MGGCN_TC_LAUNCH(128, true) : MGGCN_TC_LAUNCH(128, false);
 #undef MGGCN_TC_LAUNCH
