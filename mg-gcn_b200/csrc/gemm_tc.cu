@@ -41,6 +41,8 @@ int g_gemm_split = 0;    // 0: hi = rna_tf32(x), lo = rna_tf32(x - hi);  1: hi =
                          //    lo = x - hi left as it is (the tensor core drops its low bits): a third of the ALU work
 int g_gemm_presplit = 1; // a small B operand (the weights of H*W and G*W^T) is split once per call into hi / lo arrays
                          //    in the workspace and both halves arrive by TMA: the splitter warps only handle A
+int g_gemm_stages = 0;   // experiments: ring slots in use (0 = all), tile width override (0 = by N)
+int g_gemm_bn = 0;
 int g_gemm_ts = 1;       // A's hi / lo halves in tensor memory (TS form, see cfg); 0 = both operands in shared memory
 }  // namespace mggcn
 
@@ -85,6 +87,7 @@ struct tc_args {
     int64_t kchunk;    // multiple of BK
     int mt, nt;        // tiles along M, N
     int kgroup;
+    int stages;        // > 0: use only this many slots of the shared-memory ring (mggcn_tune "gemm_stages")
     int split_mode;    // g_gemm_split
     int b_presplit;    // B's hi / lo halves sit behind each other in the workspace and arrive as one box of mapB
     int a_one, b_one;  // an MN-major operand whose extent is a multiple of 32 arrives as ONE 3-D box per k-block
@@ -148,6 +151,16 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map
         "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
         ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
         : "memory");
+}
+// one lane of a converged warp (the same lane for the same mask every time)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -282,6 +295,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     auto b_lo = [&](int s) { return base + s * C::STAGE_BYTES + C::A_BYTES + C::B_TILE_BYTES; };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nst = g.stages > 0 && g.stages < C::STAGES ? g.stages : C::STAGES;  // ring depth in use (experiments)
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
@@ -353,13 +367,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     } else {
                         tma_load_2d(b_hi(s), &mapB, bar_full(s), k0, n0);
                     }
-                    if (++s == C::STAGES) { s = 0; ph ^= 1u; }
+                    if (++s == nst) { s = 0; ph ^= 1u; }
                 }
             }
         }
     } else if (warp == 1) {
         // ================= MMA issuer =================
-        if (lane == 0) {
+        // The WHOLE warp walks the loop with warp-uniform state and one elected lane issues: operands that the
+        // compiler can prove uniform live in uniform registers.  Under `if (lane == 0)` every tcgen05.mma was wrapped
+        // in an ELECT + 4 x R2UR.BROADCAST + branch sequence (per-thread registers -> uniform operands), about
+        // 140 cycles per instruction against 60 of tensor-pipe time: the issuing thread, not the tensor core, not
+        // shared memory and not the ring depth, bounded the kernel (profiles/r02_gemm_what_bounds_it.txt).
+        {
+            const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);  // provably uniform copy
             // instruction descriptor (cute::UMMA::InstrDescriptor): D=f32 [4,6), A=tf32 [7,10), B=tf32 [10,13),
             // a_major [15], b_major [16], N>>3 [17,23), M>>4 [24,29)
             // (a TMEM A operand is always K-major: lane = row, column = k)
@@ -390,24 +410,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 #pragma unroll
                             for (int k = 0; k < BK / UK; ++k) {
                                 const uint64_t bo = (uint64_t)((k * B_STEP) >> 4);
-                                tc_mma_tf32_ts(d_tmem, tl + (uint32_t)(k * UK), bh + bo, idesc, (kb > kg || k > 0) ? 1u : 0u);
-                                tc_mma_tf32_ts(d_tmem, th + (uint32_t)(k * UK), bl + bo, idesc, 1u);
-                                tc_mma_tf32_ts(d_tmem, th + (uint32_t)(k * UK), bh + bo, idesc, 1u);
+                                if (elect_one()) {
+                                    tc_mma_tf32_ts(d_tmem, tl + (uint32_t)(k * UK), bh + bo, idesc, (kb > kg || k > 0) ? 1u : 0u);
+                                    tc_mma_tf32_ts(d_tmem, th + (uint32_t)(k * UK), bl + bo, idesc, 1u);
+                                    tc_mma_tf32_ts(d_tmem, th + (uint32_t)(k * UK), bh + bo, idesc, 1u);
+                                }
                             }
                         } else {
                             const uint64_t ah = smem_desc(a_hi(s), A_LBO, A_SBO, A_LAY), al = smem_desc(a_lo(s), A_LBO, A_SBO, A_LAY);
 #pragma unroll
                             for (int k = 0; k < BK / UK; ++k) {
                                 const uint64_t ao = (uint64_t)((k * A_STEP) >> 4), bo = (uint64_t)((k * B_STEP) >> 4);
-                                tc_mma_tf32(d_tmem, al + ao, bh + bo, idesc, (kb > kg || k > 0) ? 1u : 0u);
-                                tc_mma_tf32(d_tmem, ah + ao, bl + bo, idesc, 1u);
-                                tc_mma_tf32(d_tmem, ah + ao, bh + bo, idesc, 1u);
+                                if (elect_one()) {
+                                    tc_mma_tf32(d_tmem, al + ao, bh + bo, idesc, (kb > kg || k > 0) ? 1u : 0u);
+                                    tc_mma_tf32(d_tmem, ah + ao, bl + bo, idesc, 1u);
+                                    tc_mma_tf32(d_tmem, ah + ao, bh + bo, idesc, 1u);
+                                }
                             }
                         }
-                        tc_commit(bar_empty(s));  // smem stage may be refilled once these MMAs have read it
-                        if (++s == C::STAGES) { s = 0; ph ^= 1u; }
+                        // (the elected lane is the same one every time: commits track the MMAs that lane issued)
+                        if (elect_one()) tc_commit(bar_empty(s));  // smem stage may be refilled once these MMAs have read it
+                        __syncwarp();
+                        if (++s == nst) { s = 0; ph ^= 1u; }
                     }
-                    tc_commit(bar_tfull(a));      // accumulator chain complete
+                    if (elect_one()) tc_commit(bar_tfull(a));      // accumulator chain complete
+                    __syncwarp();
                     if (++a == 2) { a = 0; aph ^= 1u; }
                 }
             }
@@ -477,7 +504,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 if constexpr (TS) tc_fence_before();                          // tcgen05.st -> the issuer's tcgen05.mma
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_conv(s));
-                if (++s == C::STAGES) { s = 0; ph ^= 1u; }
+                if (++s == nst) { s = 0; ph ^= 1u; }
             }
         }
     } else {
@@ -746,7 +773,7 @@ size_t gemm_tc_workspace_bytes(int ta, int tb, int64_t M, int64_t N, int64_t K) 
 int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, float alpha, const float *A, int64_t lda,
             const float *B, int64_t ldb, float beta, float *C, int64_t ldc, const mggcn_epilogue &epi, void *ws,
             size_t ws_bytes) {
-    const int bn = N <= 64 ? 64 : 128;
+    const int bn = g_gemm_bn == 64 || g_gemm_bn == 128 ? g_gemm_bn : N <= 64 ? 64 : 128;
     split_plan sp = plan_split(ta, M, N, K, bn);
     if (sp.nz > 1 && (!ws || ws_bytes < (size_t)sp.nz * M * N * sizeof(float))) {
         sp.nz = 1;
@@ -814,6 +841,7 @@ int gemm_tc(cudaStream_t st, int ta, int tb, int64_t M, int64_t N, int64_t K, fl
     g.mt = (int)((M + BM - 1) / BM);
     g.nt = (int)((N + bn - 1) / bn);
     g.kgroup = std::max(1, g_gemm_kgroup);
+    g.stages = g_gemm_stages;
     g.split_mode = g_gemm_split;
     g.b_presplit = presplit ? 1 : 0;
     g.a_one = a_one ? 1 : 0;

@@ -31,7 +31,7 @@
 using namespace mggcn;
 
 namespace mggcn {
-extern int g_gemm_tc, g_gemm_kgroup, g_gemm_split, g_gemm_presplit, g_gemm_ts;  // gemm_tc.cu
+extern int g_gemm_tc, g_gemm_kgroup, g_gemm_split, g_gemm_presplit, g_gemm_ts, g_gemm_stages, g_gemm_bn;  // gemm_tc.cu
 extern int g_skip_exchange;           // engine.cu
 extern int g_xstreams, g_xpull, g_h2d_sm, g_xgroups;  // engine.cu
 }
@@ -1078,6 +1078,8 @@ int mggcn_tune(const char *key, int value) {
     else if (!strcmp(key, "gemm_split")) slot = &mggcn::g_gemm_split;
     else if (!strcmp(key, "gemm_presplit")) slot = &mggcn::g_gemm_presplit;
     else if (!strcmp(key, "gemm_ts")) slot = &mggcn::g_gemm_ts;
+    else if (!strcmp(key, "gemm_stages")) slot = &mggcn::g_gemm_stages;
+    else if (!strcmp(key, "gemm_bn")) slot = &mggcn::g_gemm_bn;
     else if (!strcmp(key, "skip_exchange")) slot = &mggcn::g_skip_exchange;
     else if (!strcmp(key, "xstreams")) slot = &mggcn::g_xstreams;
     else if (!strcmp(key, "xpull")) slot = &mggcn::g_xpull;
