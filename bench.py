@@ -80,6 +80,7 @@ def parse():
     ap.add_argument("--cpu-repeats", type=int, default=1)
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-parity", action="store_true", help="no 10-epoch loss curve / reference run (experiments only)")
+    ap.add_argument("--e2e-variants", action="store_true", help="also time the end-to-end step with the SM-driven input copy (always on at N > 1)")
     ap.add_argument("--skip-exposed", action="store_true", help="no exposed-communication measurement at N > 1")
     ap.add_argument("--tune", nargs="*", default=[], help="key=value kernel knobs (mggcn_tune), experiments only")
     a = ap.parse_args()
@@ -630,6 +631,26 @@ def main():
     eng.sync()
     h2d_s = (time.perf_counter() - h0) / 3
     h2d_bytes_rank = Xl.numel() * 4 + Yl.numel() * 4
+    # what the input copy costs when every rank copies at once: slowest and fastest rank (the ranks share PCIe
+    # switches and one host memory system), and the same pipelined step with the copy done by a few CTAs reading
+    # the pinned rows over PCIe (mggcn_tune "h2d_sm") instead of by a copy engine
+    e2e_diag = None
+    if P > 1 or args.e2e_variants:
+        t = torch.tensor([h2d_s, -h2d_s], device="cuda", dtype=torch.float64)
+        if P > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_diag = {"h2d_alone_GBps_slowest_rank": h2d_bytes_rank / float(t[0]) / 1e9,
+                    "h2d_alone_GBps_fastest_rank": h2d_bytes_rank / -float(t[1]) / 1e9, "step_ms": {"copy_engine": e2e_wall}}
+        tuned = dict(kv.split("=") for kv in args.tune)
+        for key, val in (("h2d_chunk_kb", 256), ("h2d_chunk_kb", 2048), ("h2d_sm", 16)):
+            mg.lib().mggcn_tune(key.encode(), val)
+            eng.set_inputs(Xl, Yl, async_=2)
+            e2e_step()
+            _, w = timed(e2e_step, args.steps)
+            e2e_diag["step_ms"][f"{key}={val}"] = w
+            mg.lib().mggcn_tune(key.encode(), int(tuned.get(key, 0)))
+        eng.set_inputs(Xl, Yl, async_=2)
+        e2e_step()
 
     # ---- dominant kernel, live: eager pass with the engine's named timers (CUDA events on its stream)
     eng.set_mode(use_graph=False, timers=True)
@@ -654,6 +675,7 @@ def main():
         keys = [f"{l}_0_matmul-spmm" for l in dom_layers]
         dom_nnz = fwd.nnz
         alg = spmm_alg_bytes(n_loc, N, dom_nnz, F)
+        dom_cols = N
         scope = "whole matrix" if P == 1 else f"block row {n_loc}x{N}, own block + one gathered launch"
     else:
         # per-stage launches: the own-block launch (stage / group 0), one n_loc x n_loc block
@@ -661,6 +683,7 @@ def main():
         blk = fwd.block_rows(np.array([0, n_loc], np.uint32), cuts, only_row=0)[rank]
         dom_nnz = blk.nnz
         alg = spmm_alg_bytes(n_loc, n_loc, dom_nnz, F)
+        dom_cols = n_loc
         scope = f"own {n_loc}x{n_loc} block (first launch of the aggregation)"
     dom = [med[k] for k in keys if k in med]
     dom_ms = float(np.mean(dom)) if dom else float("nan")
@@ -677,6 +700,20 @@ def main():
     except (OSError, ValueError):
         pass
     achieved = alg / (dom_ms * 1e-3) / 1e9 if dom_ms == dom_ms and dom_ms > 0 else None
+    # second roofline: rows of B are gathered avg-degree times, and when B fits the L2 that stream (nnz*F*4 bytes)
+    # is bounded by the L2 -> SM read bandwidth (measured on B200 by tools/l2_peak.py, kept in profiles/l2_peak.json)
+    l2_roof = None
+    try:
+        l2pk = json.load(open(os.path.join(ROOT, "profiles", "l2_peak.json")))
+        if dom_ms == dom_ms and dom_ms > 0 and l2pk.get("read_GBps"):
+            gat = dom_nnz * F * 4 / (dom_ms * 1e-3) / 1e9
+            l2_roof = {"bound": "l2", "achieved": gat, "peak": float(l2pk["read_GBps"]), "unit": "GB/s",
+                       "frac": gat / float(l2pk["read_GBps"]), "peak_source": "profiles/l2_peak.json (tools/l2_peak.py on B200)",
+                       "applies": bool(dom_cols * F * 4 <= 126e6),
+                       "note": "gather stream nnz*F*4 over the launch time against the measured L2->SM read bandwidth; "
+                               "applies when B (cols*F*4 bytes) is L2-resident, else the gathers are DRAM reads"}
+    except (OSError, ValueError):
+        pass
     spmm_ms = sum(v for k, v in med.items() if k.endswith("matmul-spmm"))
     gemm_ms = sum(v for k, v in med.items() if k.endswith("matmul-gemm"))
     xfer_ms = sum(v for k, v in med.items() if k.endswith("matmul-bcast"))
@@ -721,7 +758,8 @@ def main():
         "parity": parity,
         "e2e": {"value": e2e_wall, "unit": "ms/epoch", "device_ms": e2e_dev,
                 "h2d_bytes_per_step": int(N * F_in * 4 + N * 4), "d2h_bytes_per_step": 16 * P,
-                "h2d_GBps_per_rank_all_ranks_copying": h2d_bytes_rank / h2d_s / 1e9, "numa_local_cpus": numa_cpus},
+                "h2d_GBps_per_rank_all_ranks_copying": h2d_bytes_rank / h2d_s / 1e9, "numa_local_cpus": numa_cpus,
+                **({"diag": e2e_diag} if e2e_diag else {})},
         "synced_epoch": {"value": ms_sync_wall, "device_ms": ms_sync_dev,
                          "note": "epoch + loss read-back + host sync every step, like the reference's loop (src/main.cpp:158-169)"},
         "gpu_launches": int(launches),
@@ -733,6 +771,7 @@ def main():
                      "alg_bytes_per_launch": alg, "launch_ms": dom_ms,
                      "gather_GBps": (dom_nnz * F * 4 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 else None,
                      "GFLOPs": (2 * dom_nnz * F / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 else None,
+                     "l2": l2_roof,
                      "note": "achieved/frac use the algorithmic bytes of ONE pass over the operands (SURVEY.md 8d) and "
                              "launch_ms is the whole aggregation (all its windows / blocks); gather_GBps = nnz*F*4/t is "
                              "the operand traffic the L2 has to serve when B is gathered avg-degree times"},

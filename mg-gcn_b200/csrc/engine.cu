@@ -40,6 +40,8 @@ int g_xstreams = 2;
 int g_xpull = 0;
 // > 0: set_inputs reads pinned host rows with that many CTAs of pull_copy_kernel instead of a copy-engine transfer
 int g_h2d_sm = 0;
+// > 0: a contiguous host -> device input transfer is issued in pieces of this many KB (see copy_rows_in)
+int g_h2d_chunk_kb = 0;
 // grouping of the stages of the grouped exchange: 0 = by the shape (see choose_groups), 1 = one launch per stage,
 // 2 = own | 1 | 2-3 | 4-7 | ...
 int g_xgroups = 0;
@@ -1213,7 +1215,13 @@ static int copy_rows_in(float *dst, int64_t ld, const float *src, int64_t width,
         cudaGetLastError();
     }
     if (ld == width) {
-        MGGCN_CUDA_TRY(cudaMemcpyAsync(dst, src, (size_t)rows * (size_t)width * 4, cudaMemcpyDefault, st));
+        // g_h2d_chunk_kb > 0: the transfer is cut into pieces so that a copy engine it shares with the peer pulls of a
+        // running epoch can take a (higher-priority) pull between two pieces instead of behind the whole transfer
+        const size_t total = (size_t)rows * (size_t)width * 4;
+        const size_t piece = g_h2d_chunk_kb > 0 ? (size_t)g_h2d_chunk_kb << 10 : total;
+        for (size_t off = 0; off < total; off += piece)
+            MGGCN_CUDA_TRY(cudaMemcpyAsync(reinterpret_cast<char *>(dst) + off, reinterpret_cast<const char *>(src) + off,
+                                           std::min(piece, total - off), cudaMemcpyDefault, st));
     } else {
         MGGCN_CUDA_TRY(cudaMemcpy2DAsync(dst, (size_t)ld * 4, src, (size_t)width * 4, (size_t)width * 4, (size_t)rows,
                                          cudaMemcpyDefault, st));
