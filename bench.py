@@ -81,6 +81,7 @@ def parse():
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-parity", action="store_true", help="no 10-epoch loss curve / reference run (experiments only)")
     ap.add_argument("--e2e-variants", action="store_true", help="also time the end-to-end step with the SM-driven input copy (always on at N > 1)")
+    ap.add_argument("--e2e-sweep", nargs="*", default=[], help="knob combinations 'k=v,k=v' timed resident and end to end (experiments)")
     ap.add_argument("--skip-exposed", action="store_true", help="no exposed-communication measurement at N > 1")
     ap.add_argument("--tune", nargs="*", default=[], help="key=value kernel knobs (mggcn_tune), experiments only")
     a = ap.parse_args()
@@ -399,6 +400,9 @@ def run_reference(args, mg, rank):
 
 
 # ------------------------------------------------------------------------------------------------
+DEFAULT_TUNE = {}   # library defaults of the knobs --e2e-sweep restores, where they are not 0
+
+
 def pin_to_gpu_numa_node(local):
     """Pinned staging buffers should live on the NUMA node the GPU hangs off (first touch by this process):
     restrict the process to the CPUs NVML reports as local to the GPU.  Best effort."""
@@ -640,15 +644,63 @@ def main():
         if P > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_diag = {"h2d_alone_GBps_slowest_rank": h2d_bytes_rank / float(t[0]) / 1e9,
-                    "h2d_alone_GBps_fastest_rank": h2d_bytes_rank / -float(t[1]) / 1e9, "step_ms": {"copy_engine": e2e_wall}}
+                    "h2d_alone_GBps_fastest_rank": h2d_bytes_rank / -float(t[1]) / 1e9,
+                    "step_ms": {"default (pieces by size, see h2d_piece_bytes)": e2e_wall}}
         tuned = dict(kv.split("=") for kv in args.tune)
-        for key, val in (("h2d_chunk_kb", 256), ("h2d_chunk_kb", 2048), ("h2d_sm", 16)):
+        for key, val in (("h2d_chunk_kb", 1 << 22), ("h2d_chunk_kb", 128), ("h2d_chunk_kb", 512)):
             mg.lib().mggcn_tune(key.encode(), val)
             eng.set_inputs(Xl, Yl, async_=2)
             e2e_step()
             _, w = timed(e2e_step, args.steps)
             e2e_diag["step_ms"][f"{key}={val}"] = w
             mg.lib().mggcn_tune(key.encode(), int(tuned.get(key, 0)))
+        # the two sides of the pipelined step, loaded by each other: a foreign stream keeps copying X from pinned
+        # memory while the resident-input epoch is timed, and the copies are timed while the epochs run
+        try:
+            cs = torch.cuda.Stream()
+            dst = torch.empty(Xl.shape, dtype=Xl.dtype, device="cuda")
+            ncp = 2 * args.steps
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(ncp + 1)]
+            barrier()
+            with torch.cuda.stream(cs):
+                evs[0].record(cs)
+                for i in range(ncp):
+                    dst.copy_(Xl, non_blocking=True)
+                    evs[i + 1].record(cs)
+            ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ea.record(sc)
+            for _ in range(args.steps):
+                eng.epoch(**ADAM)
+            eb.record(sc)
+            eng.sync()
+            torch.cuda.synchronize()
+            t = torch.tensor([ea.elapsed_time(eb) / args.steps,
+                              float(np.median([evs[i].elapsed_time(evs[i + 1]) for i in range(max(1, args.steps // 2))]))],
+                             device="cuda", dtype=torch.float64)
+            if P > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_diag["loaded"] = {"epoch_ms_while_copying": float(t[0]), "copy_ms_while_computing_slowest_rank": float(t[1]),
+                                  "copy_ms_alone_slowest_rank": e2e_diag and h2d_bytes_rank / (e2e_diag["h2d_alone_GBps_slowest_rank"] * 1e9) * 1e3}
+            del dst
+        except Exception as ex:  # diagnostics only
+            e2e_diag["loaded"] = {"error": repr(ex)}
+        # combinations of exchange / copy knobs, each timed with resident inputs and end to end (the captured epoch
+        # is re-recorded when an exchange knob changes)
+        for combo in args.e2e_sweep:
+            kv = [x.split("=") for x in combo.split(",")]
+            for k, v in kv:
+                mg.lib().mggcn_tune(k.encode(), int(v))
+            for _ in range(3):
+                eng.epoch(**ADAM)
+            dv, _ = timed(lambda: eng.epoch(**ADAM), args.steps)
+            eng.set_inputs(Xl, Yl, async_=2)
+            e2e_step()
+            _, w = timed(e2e_step, args.steps)
+            e2e_diag.setdefault("sweep", {})[combo] = {"value_ms": dv, "e2e_ms": w}
+            for k, v in kv:
+                mg.lib().mggcn_tune(k.encode(), int(tuned.get(k, DEFAULT_TUNE.get(k, 0))))
+        for _ in range(3):
+            eng.epoch(**ADAM)
         eng.set_inputs(Xl, Yl, async_=2)
         e2e_step()
 

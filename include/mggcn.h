@@ -145,7 +145,9 @@ MGGCN_API size_t mggcn_spmm_plan_workspace_bytes(const mggcn_spmm_plan_t *plan, 
 MGGCN_API void mggcn_spmm_plan_destroy(mggcn_spmm_plan_t *plan);
 /* Tuning knobs for experiments ("unroll", "threads", "policy", "split", "slices", "blocks", "blocks_model", "window",
  * "tile_mb", "tma", "narrow", "gemm_tc", "gemm_kgroup", "skip_exchange", "xstreams" = streams a peer block is split
- * over, "xpull" = SM-driven peer pulls, "h2d_sm" = CTAs reading pinned inputs instead of a copy-engine transfer);
+ * over (0 = by the block size), "xpull" = SM-driven peer pulls, "h2d_sm" = CTAs reading pinned inputs instead of a
+ * copy-engine transfer, "h2d_chunk_kb" = size of the pieces an input transfer is issued in (0 = by size on multi-GPU
+ * engines, so that peer pulls of the running epoch are not queued behind the whole transfer));
  * a negative value only queries.
  * Returns the old value or MGGCN_E_INVALID for an unknown key. */
 MGGCN_API int mggcn_tune(const char *key, int value);

@@ -110,6 +110,10 @@ class repl_dn_matrix {
             detail::stream_wait_stream(ctx[j], ctx[j].stream(0), ctx[0], ctx[0].stream(0));
             CHECK_CUDA(cudaMemcpyPeerAsync(As[j].buffer(), (int)j, As[0].buffer(), 0, As[0].size() * sizeof(r_t), ctx[j].stream(0)));
         }
+        // write-after-read: GPU 0 may not touch its replica again before every peer has read it (Adam adds
+        // weight_decay * W to G_W in place right after the all-reduce of the last layer's gradient; a peer that
+        // copied late would see that term and add it a second time)
+        for (std::size_t j = 1; j < size(); ++j) detail::stream_wait_stream(ctx[0], ctx[0].stream(0), ctx[j], ctx[j].stream(0));
     }
 
    public:

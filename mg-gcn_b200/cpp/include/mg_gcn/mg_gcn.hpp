@@ -68,12 +68,20 @@ inline bool have_device() {
 // Host-indexable buffers, like the reference's cudaMallocManaged containers (src/mg_gcn.hpp:74-82):
 // callers index matrices on the host (operator[]) and hand the same pointer to kernels.  Without a
 // device the allocation is plain host memory so that the host half of the surface still works.
+// MGGCN_POISON=1 fills every new buffer with 0xFF bytes (NaN as float): a read of memory nobody wrote shows up as
+// NaN instead of depending on what the previous process left in device memory (debugging aid of the surface tests)
+inline bool poison_allocations() {
+    static const bool on = std::getenv("MGGCN_POISON") != nullptr;
+    return on;
+}
+
 template <typename T>
 cuda_ptr<T> cuda_malloc_managed(std::size_t count) {
     if (count == 0) count = 1;
     T *p = nullptr;
     if (have_device()) {
         CHECK_CUDA(cudaMallocManaged(reinterpret_cast<void **>(&p), count * sizeof(T)));
+        if (poison_allocations()) CHECK_CUDA(cudaMemset(p, 0xFF, count * sizeof(T)));
         return cuda_ptr<T>(p, [](T *q) { cudaFree(q); });
     }
     p = static_cast<T *>(std::malloc(count * sizeof(T)));
@@ -87,6 +95,7 @@ cuda_ptr<T> cuda_malloc(std::size_t count) {
     if (count == 0) count = 1;
     T *p = nullptr;
     CHECK_CUDA(cudaMalloc(reinterpret_cast<void **>(&p), count * sizeof(T)));
+    if (poison_allocations()) CHECK_CUDA(cudaMemset(p, 0xFF, count * sizeof(T)));
     return cuda_ptr<T>(p, [](T *q) { cudaFree(q); });
 }
 

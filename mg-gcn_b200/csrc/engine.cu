@@ -36,12 +36,12 @@ namespace mggcn {
 int g_skip_exchange = 0;
 // exchange tuning: a block's pull is cut into g_xstreams row ranges issued on as many streams (one copy engine each);
 // g_xpull = 1 moves the bytes with pull_copy_kernel (SM loads over NVLink) instead of the copy engines
-int g_xstreams = 2;
+int g_xstreams = 0;  // 0 = by the block size (see peer_pull)
 int g_xpull = 0;
 // > 0: set_inputs reads pinned host rows with that many CTAs of pull_copy_kernel instead of a copy-engine transfer
 int g_h2d_sm = 0;
 // > 0: a contiguous host -> device input transfer is issued in pieces of this many KB (see copy_rows_in)
-int g_h2d_chunk_kb = 0;
+int g_h2d_chunk_kb = 0;  // 0 = by size on multi-GPU engines (h2d_piece_bytes); a value past the transfer size = one transfer
 // grouping of the stages of the grouped exchange: 0 = by the shape (see choose_groups), 1 = one launch per stage,
 // 2 = own | 1 | 2-3 | 4-7 | ...
 int g_xgroups = 0;
@@ -430,7 +430,12 @@ int peer_pull(eng *e, int blk, size_t off, float *dst, size_t rows, size_t ld) {
     if (g_skip_exchange) return MGGCN_OK;  // measurement only
     const char *src = e->peer_arena[blk] + off;
     const bool by_sm = g_xpull || (e->peer_inproc[blk] && !e->capturing);
-    int nx = std::min(g_xstreams, (int)mggcn_engine::kXStreams);
+    // Large blocks travel as two halves on two engines (one engine does not fill the link: products- and
+    // papers100M-shape, 2 GPUs at reddit shape); small blocks of a many-rank exchange, where several pulls are in
+    // flight anyway, are faster whole (8 GPUs, reddit shape, 15 MB blocks: 3.18 ms/epoch with 1 stream, 3.31 with 2,
+    // 3.82 with 4; profiles/r02_bench_reddit_n8_e2e_sweep.json)
+    const int want = g_xstreams > 0 ? g_xstreams : (rows * ld * sizeof(float) <= ((size_t)16 << 20) ? 1 : 2);
+    int nx = std::min(want, (int)mggcn_engine::kXStreams);
     nx = std::max(1, std::min(nx, (int)(rows / 1024) + 1));
     if (e->sm == e->sc || by_sm) nx = 1;  // no overlap: everything on the compute stream; SM pulls fill the link alone
     if (nx > 1) MGGCN_CUDA_TRY(cudaEventRecord(e->ev_xfork, e->sm));
@@ -1200,7 +1205,19 @@ int mggcn_engine_set_adjacency(mggcn_engine_t *e, int which, const uint64_t *con
 }
 
 // host rows (pitch = width floats) into device rows of pitch ld: one flat copy when the pitches agree
-static int copy_rows_in(float *dst, int64_t ld, const float *src, int64_t width, int64_t rows, cudaStream_t st) {
+// Size of the pieces a contiguous host -> device input transfer is issued in.  On a multi-GPU engine the transfer
+// shares the copy engines with the peer pulls of the running epoch; behind ONE 71 MB transfer the pulls of a whole
+// epoch queued up (8 GPUs, reddit shape: the epoch ran 7.4 ms instead of 3.3 while a foreign stream copied, the
+// pipelined step 5.4 ms).  In 256 KB pieces the engine takes the (higher-priority) pulls in between: 3.8 ms
+// (profiles/r02_bench_reddit_n8_e2e_sweep.json).  At most 256 pieces, so the host side stays below a millisecond.
+static size_t h2d_piece_bytes(size_t total, int P) {
+    if (g_h2d_chunk_kb > 0) return (size_t)g_h2d_chunk_kb << 10;
+    if (P <= 1) return total;
+    const size_t piece = std::max<size_t>((size_t)256 << 10, (total + 255) / 256);
+    return (piece + 65535) & ~(size_t)65535;
+}
+
+static int copy_rows_in(float *dst, int64_t ld, const float *src, int64_t width, int64_t rows, cudaStream_t st, int P) {
     if (g_h2d_sm && ld == width && ((size_t)rows * (size_t)width) % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
         // pinned host memory is mapped into the device's address space: a few CTAs reading it with 128-bit loads
         // keep PCIe full and leave the copy engines to the peer exchange (an H2D transfer and the pulls of an
@@ -1215,10 +1232,8 @@ static int copy_rows_in(float *dst, int64_t ld, const float *src, int64_t width,
         cudaGetLastError();
     }
     if (ld == width) {
-        // g_h2d_chunk_kb > 0: the transfer is cut into pieces so that a copy engine it shares with the peer pulls of a
-        // running epoch can take a (higher-priority) pull between two pieces instead of behind the whole transfer
         const size_t total = (size_t)rows * (size_t)width * 4;
-        const size_t piece = g_h2d_chunk_kb > 0 ? (size_t)g_h2d_chunk_kb << 10 : total;
+        const size_t piece = std::max<size_t>(1, h2d_piece_bytes(total, P));
         for (size_t off = 0; off < total; off += piece)
             MGGCN_CUDA_TRY(cudaMemcpyAsync(reinterpret_cast<char *>(dst) + off, reinterpret_cast<const char *>(src) + off,
                                            std::min(piece, total - off), cudaMemcpyDefault, st));
@@ -1243,7 +1258,7 @@ int mggcn_engine_set_inputs(mggcn_engine_t *e, const float *X_host, const int32_
             MGGCN_CUDA_TRY(cudaEventCreateWithFlags(&e->ev_swap, cudaEventDisableTiming));
         }
         if (e->swap_recorded) MGGCN_CUDA_TRY(cudaStreamWaitEvent(e->scopy, e->ev_swap, 0));  // WAR on the shadows
-        if (X_host) TRY(copy_rows_in(e->X_shadow, e->ldX, X_host, e->sizes[0], e->n, e->scopy));
+        if (X_host) TRY(copy_rows_in(e->X_shadow, e->ldX, X_host, e->sizes[0], e->n, e->scopy, e->P));
         if (Y_host) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y_shadow, Y_host, (size_t)e->n * 4, cudaMemcpyDefault, e->scopy));
         MGGCN_CUDA_TRY(cudaEventRecord(e->ev_pref, e->scopy));
         e->pref_x = e->pref_x || X_host;
@@ -1252,7 +1267,7 @@ int mggcn_engine_set_inputs(mggcn_engine_t *e, const float *X_host, const int32_
     }
     // ordered after everything already queued on the compute stream (the previous epoch reads X)
     cudaStream_t st = e->sc;
-    if (X_host) TRY(copy_rows_in(e->X, e->ldX, X_host, e->sizes[0], e->n, st));
+    if (X_host) TRY(copy_rows_in(e->X, e->ldX, X_host, e->sizes[0], e->n, st, e->P));
     if (Y_host) MGGCN_CUDA_TRY(cudaMemcpyAsync(e->Y, Y_host, (size_t)e->n * 4, cudaMemcpyDefault, st));
     if (!async) MGGCN_CUDA_TRY(cudaStreamSynchronize(st));
     return MGGCN_OK;
