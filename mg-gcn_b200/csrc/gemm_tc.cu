@@ -37,8 +37,11 @@ using namespace mggcn;
 namespace mggcn {
 int g_gemm_tc = 1;       // 0: never use this path (mggcn_tune "gemm_tc")
 int g_gemm_kgroup = 2;   // k-blocks per tensor-core accumulation chain (mggcn_tune "gemm_kgroup")
-int g_gemm_split = 0;    // 0: hi = rna_tf32(x), lo = rna_tf32(x - hi);  1: hi = x with the low 13 mantissa bits cleared,
-                         //    lo = x - hi left as it is (the tensor core drops its low bits): a third of the ALU work
+int g_gemm_split = 1;    // 0: hi = rna_tf32(x), lo = rna_tf32(x - hi);  1 (default): hi = x with the low 13 mantissa bits
+                         //    cleared, lo = x - hi left as it is (the tensor core drops its low bits).  The two cvt.rna
+                         //    per element run on the XU pipe (16 lanes per SM), which the splitter warps saturate; AND +
+                         //    FADD do not: 0.978 -> 0.909 ms over the eight reddit-shape products, max error 3.2e-7 ->
+                         //    5.5e-7 of the result's largest entry (profiles/r02_gemm_split_modes.jsonl)
 int g_gemm_presplit = 1; // a small B operand (the weights of H*W and G*W^T) is split once per call into hi / lo arrays
                          //    in the workspace and both halves arrive by TMA: the splitter warps only handle A
 int g_gemm_stages = 0;   // experiments: ring slots in use (0 = all), tile width override (0 = by N)
