@@ -380,7 +380,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         // compiler can prove uniform live in uniform registers.  Under `if (lane == 0)` every tcgen05.mma was wrapped
         // in an ELECT + 4 x R2UR.BROADCAST + branch sequence (per-thread registers -> uniform operands), about
         // 140 cycles per instruction against 60 of tensor-pipe time: the issuing thread, not the tensor core, not
-        // shared memory and not the ring depth, bounded the kernel (profiles/r02_gemm_what_bounds_it.txt).
+        // shared memory and not the ring depth, bounded the kernel (profiles/r02_ncu_gemm_tc_ts_form.txt and the stage / tile-width sweeps of round 2).
         {
             const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);  // provably uniform copy
             // instruction descriptor (cute::UMMA::InstrDescriptor): D=f32 [4,6), A=tf32 [7,10), B=tf32 [10,13),
