@@ -33,7 +33,7 @@ using namespace mggcn;
 namespace mggcn {
 extern int g_gemm_tc, g_gemm_kgroup, g_gemm_split, g_gemm_presplit, g_gemm_ts, g_gemm_stages, g_gemm_bn;  // gemm_tc.cu
 extern int g_skip_exchange;           // engine.cu
-extern int g_xstreams, g_xpull, g_h2d_sm, g_h2d_chunk_kb, g_xgroups;  // engine.cu
+extern int g_xstreams, g_xpull, g_h2d_sm, g_h2d_chunk_kb, g_input_flip, g_xgroups;  // engine.cu
 }
 
 namespace {
@@ -1086,6 +1086,7 @@ int mggcn_tune(const char *key, int value) {
     else if (!strcmp(key, "xgroups")) slot = &mggcn::g_xgroups;
     else if (!strcmp(key, "h2d_sm")) slot = &mggcn::g_h2d_sm;
     else if (!strcmp(key, "h2d_chunk_kb")) slot = &mggcn::g_h2d_chunk_kb;
+    else if (!strcmp(key, "input_flip")) slot = &mggcn::g_input_flip;
     if (!slot) return fail(MGGCN_E_INVALID, "unknown tuning key %s", key);
     const int old = *slot;
     if (slot == &g_threads && (value < 32 || value > 256 || value % 32)) return fail(MGGCN_E_INVALID, "threads must be 32..256");
