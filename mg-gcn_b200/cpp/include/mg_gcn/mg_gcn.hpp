@@ -114,6 +114,10 @@ inline void prefetch_to_device(const void *p, std::size_t bytes, int device, cud
 #else
     cudaMemPrefetchAsync(p, bytes, device, st);
 #endif
+    // The migration is finished before anything else is queued: the callers are constructors (scatter of a dataset,
+    // block split), and the first consumers of these ranges are copy-engine pulls from ANOTHER device and TMA loads,
+    // which should not have to race a migration still in flight on the default stream.
+    cudaStreamSynchronize(st);
     cudaGetLastError();
 }
 
