@@ -175,6 +175,25 @@ MGGCN_API size_t mggcn_gemm_workspace_bytes(int ta, int tb, int64_t M, int64_t N
 MGGCN_API int mggcn_colsum_f32(mggcn_stream_t stream, int64_t rows, int64_t N, const float *G,
                                int64_t ldg, float *out, void *ws, size_t ws_bytes);
 MGGCN_API size_t mggcn_colsum_workspace_bytes(int64_t rows, int64_t N);
+/* Column sums for callers that cannot provide a workspace.  (No counterpart in the reference: it has no
+ * allocation-free path at all -- its G_b is a cublasSgemm against a ones row on buffers the layer object
+ * cudaMalloc'ed in its constructor.)
+ * Who needs it: code that runs where device allocation is off the table -- a host application that handed the whole
+ * GPU to its own memory manager and gives plug-ins no allocator, a callback or a capture region in which cudaMalloc
+ * is illegal, a latency-bound loop that cannot take the device-wide synchronisation cudaMalloc / cudaFree imply.
+ * mggcn_colsum_f32 pushes that problem to the caller (`ws`); this variant keeps the partial sums in a fixed
+ * array compiled into the library instead, and calls no cudaMalloc, cudaFree or allocating routine, ever.
+ *   Limit: N <= 1024 columns (any number of rows); a wider G returns MGGCN_E_INVALID with nothing enqueued.
+ *   Cost: the array is 592 x 1024 floats = 2,424,832 bytes of device memory on every GPU that loads this
+ *         library, held until the process exits whether or not this entry point is ever called.
+ *   Device: the device that owns `stream` must be current.  The first call on a device resolves the array's
+ *         device address (cudaGetSymbolAddress); make that first call before any stream capture starts.
+ *   Sharing: every call on a GPU uses the same array.  It still holds the previous call's partials -- harmless,
+ *         each call overwrites every entry it later reads -- but two calls that overlap on the GPU (two streams,
+ *         two host threads) race on it and both results are garbage; the caller must order them.
+ * G, ldg, out and the result are exactly those of mggcn_colsum_f32 (same kernels, same summation order). */
+MGGCN_API int mggcn_colsum_static_f32(mggcn_stream_t stream, int64_t rows, int64_t N, const float *G,
+                                      int64_t ldg, float *out);
 
 /* ------------------------------------------------------------------------------------------
  * a12. Element-wise kernels adjacent to the SpMM (stream-level mirrors of

@@ -81,6 +81,7 @@ _SIGS = {
     "mggcn_gemm_workspace_bytes": (_sz, [_i32, _i32, _i64, _i64, _i64]),
     "mggcn_colsum_f32": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _vp, _vp, _sz]),
     "mggcn_colsum_workspace_bytes": (_sz, [_i64, _i64]),
+    "mggcn_colsum_static_f32": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _vp]),
     "mggcn_leaky_relu_forward_f32": (C.c_int, [_vp, _vp, _vp, _sz, _f32]),
     "mggcn_leaky_relu_backward_f32": (C.c_int, [_vp, _vp, _vp, _vp, _sz, _f32]),
     "mggcn_broadcast_rows_f32": (C.c_int, [_vp, _vp, _vp, _sz, _sz, _i32]),

@@ -460,6 +460,41 @@ int launch_splitk_reduce(cudaStream_t st, const float *part, int nz, int64_t M, 
 }
 }  // namespace mggcn
 
+// ------------------------------------------------------------------------------------------------
+// Built-in scratch for mggcn_colsum_static_f32 (declared in include/mggcn.h, no reference counterpart).
+// The array is part of the library image: every GPU that loads libmggcn.so carries these
+// COLSUM_STATIC_MAX_PARTS x COLSUM_STATIC_MAX_N floats (2,424,832 bytes) until the process exits, used or not.
+// In host code `g_colsum_scratch` is only a handle for the runtime's symbol table, never a pointer a kernel could
+// follow -- its device address differs per GPU and is asked for once per device (colsum_static_scratch below).
+// ------------------------------------------------------------------------------------------------
+constexpr int64_t COLSUM_STATIC_MAX_N = 1024;        // widest G the entry point accepts
+constexpr int COLSUM_STATIC_MAX_PARTS = 148 * 4;     // the most stage-1 CTAs colsum_parts() ever asks for
+constexpr int COLSUM_STATIC_MAX_DEVICES = 64;
+static __device__ __align__(256) float g_colsum_scratch[(size_t)COLSUM_STATIC_MAX_PARTS * COLSUM_STATIC_MAX_N];
+
+namespace {
+std::atomic<float *> g_colsum_scratch_addr[COLSUM_STATIC_MAX_DEVICES];
+
+// Device address of g_colsum_scratch on the CURRENT device.  The first call per device asks the runtime
+// (cudaGetSymbolAddress, which also makes sure the module is loaded there); later calls read the cached pointer.
+// Two threads racing through the first call both get the same answer, so the cache needs no lock.
+int colsum_static_scratch(float **out) {
+    int dev = -1;
+    MGGCN_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= COLSUM_STATIC_MAX_DEVICES)
+        return fail(MGGCN_E_UNSUPPORTED, "colsum_static: device ordinal %d is beyond the %d this library keeps an address for",
+                    dev, COLSUM_STATIC_MAX_DEVICES);
+    float *p = g_colsum_scratch_addr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        MGGCN_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_colsum_scratch));
+        if (!p) return fail(MGGCN_E_STATE, "colsum_static: the runtime returned no address for the scratch array");
+        g_colsum_scratch_addr[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return MGGCN_OK;
+}
+}  // namespace
+
 extern "C" {
 
 size_t mggcn_gemm_workspace_bytes(int ta, int tb, int64_t M, int64_t N, int64_t K) {
@@ -594,6 +629,39 @@ int mggcn_adam_f32(mggcn_stream_t stream, size_t n, float *p, float *g, float *m
     if (!p || !g || !m || !v) return fail(MGGCN_E_INVALID, "null operand");
     adam_kernel<<<ew_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(n, p, g, m, v, lr / bc1, beta1, beta2, wd,
                                                                         eps, bc2, n_decay);
+    MGGCN_LAUNCH_CHECK();
+    return MGGCN_OK;
+}
+
+// Column sums without a workspace argument and without any allocation: the per-CTA partial rows go to the
+// library's own g_colsum_scratch.  Same two kernels, same grid and same summation order as mggcn_colsum_f32, so the
+// two entry points return the same bits.  Contract (repeated in include/mggcn.h):
+//  - N <= 1024; wider inputs are refused with MGGCN_E_INVALID before anything is enqueued;
+//  - the device that owns `stream` must be the current device of the calling thread;
+//  - the first call on each device looks the array's address up and must therefore not sit inside a stream
+//    capture; make one call per device during start-up;
+//  - nothing in the array has to be zero at launch: stage 1 stores every partial that stage 2 reads, including the
+//    rows of CTAs whose row range is empty, so what the previous call left behind is overwritten, never read;
+//  - ONE array per GPU serves all callers: two calls that may run at the same time (different streams, or different
+//    host threads of this process, on one device) overwrite each other's partials.  Order them.
+int mggcn_colsum_static_f32(mggcn_stream_t stream, int64_t rows, int64_t N, const float *G, int64_t ldg, float *out) {
+    if (rows < 0 || N < 0) return fail(MGGCN_E_INVALID, "negative dimension");
+    if (N == 0) return MGGCN_OK;
+    if (!out || (!G && rows > 0)) return fail(MGGCN_E_INVALID, "null operand");
+    if (N > COLSUM_STATIC_MAX_N)
+        return fail(MGGCN_E_INVALID, "colsum_static: N = %lld is wider than the built-in scratch serves (at most %lld columns); "
+                    "use mggcn_colsum_f32 with a caller-owned workspace", (long long)N, (long long)COLSUM_STATIC_MAX_N);
+    const int parts = colsum_parts(rows);
+    if (parts > COLSUM_STATIC_MAX_PARTS) return fail(MGGCN_E_STATE, "colsum_static: %d partial rows exceed the scratch", parts);
+    float *scratch = nullptr;
+    if (int rc = colsum_static_scratch(&scratch)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t rpc = (rows + parts - 1) / parts;
+    const bool vec4 = ldg % 4 == 0 && (reinterpret_cast<uintptr_t>(G) & 15) == 0;
+    if (vec4) colsum_stage1<true><<<parts, dim3(32, 8), 0, st>>>(G, ldg, rows, N, std::max<int64_t>(rpc, 1), scratch);
+    else colsum_stage1<false><<<parts, dim3(32, 8), 0, st>>>(G, ldg, rows, N, std::max<int64_t>(rpc, 1), scratch);
+    MGGCN_LAUNCH_CHECK();
+    colsum_stage2<<<(unsigned)((N + 31) / 32), dim3(32, 8), 0, st>>>(scratch, parts, N, out);
     MGGCN_LAUNCH_CHECK();
     return MGGCN_OK;
 }
