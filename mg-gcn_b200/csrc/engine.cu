@@ -21,6 +21,7 @@
 #include <nccl.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <cmath>
 #include <string>
 #include <vector>
@@ -943,7 +944,13 @@ int mggcn_engine_create(const mggcn_engine_config *cfg, mggcn_engine_t **out) {
     // the rank even when N % P != 0 makes the blocks uneven.
     for (int l = 0; l < e->L; ++l) {
         const layer_t &y = e->layers[l];
-        e->ws_gemm_bytes = std::max(e->ws_gemm_bytes, mggcn_gemm_workspace_bytes(1, 0, y.in, y.out, e->max_block_rows));
+        // the three products of a layer share one workspace: forward H*W (pre-split W), dW = H^T*G (split-K partials),
+        // dH = G*W^T (pre-split W); a workspace sized for dW alone made the other two fall back to in-kernel splitting
+        // whenever the partials happened to be the smaller need
+        e->ws_gemm_bytes = std::max({e->ws_gemm_bytes,
+                                     mggcn_gemm_workspace_bytes(0, 0, e->max_block_rows, y.out, y.in),
+                                     mggcn_gemm_workspace_bytes(1, 0, y.in, y.out, e->max_block_rows),
+                                     mggcn_gemm_workspace_bytes(0, 1, e->max_block_rows, y.in, y.out)});
         e->ws_colsum_bytes = std::max(e->ws_colsum_bytes, mggcn_colsum_workspace_bytes(e->max_block_rows, y.out));
     }
     e->ws_loss_bytes = mggcn_softmax_xent_workspace_bytes(e->max_block_rows);

@@ -42,6 +42,11 @@ int g_gemm_split = 1;    // 0: hi = rna_tf32(x), lo = rna_tf32(x - hi);  1 (defa
                          //    per element run on the XU pipe (16 lanes per SM), which the splitter warps saturate; AND +
                          //    FADD do not: 0.978 -> 0.909 ms over the eight reddit-shape products, max error 3.2e-7 ->
                          //    5.5e-7 of the result's largest entry (profiles/r02_gemm_split_modes.jsonl)
+                         //    The dropped terms are one-sided, but each is a fixed small fraction of its own signed
+                         //    product, so they cancel with the sum: G_W = H^T G at K = 233,000 with sum|ab| = 111 x |sum ab|
+                         //    is within 2.0e-6 (truncating) / 1.5e-6 (rna) of fp64 per entry, mean signed error 7e-9 of the
+                         //    rms (tests/test_gpu_dense.py::test_gemm_weight_gradient_under_cancellation,
+                         //    profiles/r03_gemm_split_cancellation.log) -- so the large-K path keeps the default too
 int g_gemm_presplit = 1; // a small B operand (the weights of H*W and G*W^T) is split once per call into hi / lo arrays
                          //    in the workspace and both halves arrive by TMA: the splitter warps only handle A
 int g_gemm_stages = 0;   // experiments: ring slots in use (0 = all), tile width override (0 = by N)

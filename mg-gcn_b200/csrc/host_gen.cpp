@@ -264,9 +264,10 @@ static int gen_rows(int64_t n_raw, int64_t target_directed_edges, int degree_mod
     std::vector<std::atomic<uint64_t>> cursor((size_t)nl);
     for (int64_t i = 0; i < nl; ++i) cursor[i].store(start[i], std::memory_order_relaxed);
     // pass 2: scatter from the buffers (order inside a row is arbitrary here, fixed by the sort below)
-#pragma omp parallel num_threads(T)
-    {
-        std::vector<uint64_t> &mine_buf = kept[(size_t)omp_get_thread_num()];
+    // (a loop over the T buffers, not "buffer of my thread id": this region may be given fewer threads than pass 1 had)
+#pragma omp parallel for schedule(static, 1) num_threads(T)
+    for (int t = 0; t < T; ++t) {
+        std::vector<uint64_t> &mine_buf = kept[(size_t)t];
         for (uint64_t pr : mine_buf) raw[cursor[pr >> 32].fetch_add(1, std::memory_order_relaxed)] = (uint32_t)pr;
         std::vector<uint64_t>().swap(mine_buf);
     }

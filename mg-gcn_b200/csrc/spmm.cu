@@ -774,6 +774,7 @@ int spmm_scheduled(cudaStream_t st, int64_t rows, int64_t cols, const void *rowp
         return spmm_dispatch(st, rows, cols, rowptr, rowptr64, colidx, vals, B, ldb, C, ldc, F, alpha, beta, epi, plan, nullptr, ws);
     int nwin = 0;
     char first[sizeof t_last_config];
+    first[0] = 0;  // F == 0 launches nothing
     for (int f0 = 0; f0 < F; f0 += w, ++nwin) {
         const int fw = std::min(w, F - f0);
         mggcn_epilogue e2{};

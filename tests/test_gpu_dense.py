@@ -28,6 +28,36 @@ def test_gemm_matches_fp64(mg, cuda, ta, tb, M, N, K):
     assert float(err.max()) <= 1e-5, float(err.max())
 
 
+@pytest.mark.parametrize("split", [0, 1])
+def test_gemm_weight_gradient_under_cancellation(mg, cuda, split):
+    """G_W = H^T G at a reddit-sized K with inputs whose products cancel (the truncating hi/lo split drops
+    one-sided terms, and a bar relative to sum |a||b| would hide what that does to a sum that nearly cancels).
+    H is sign-mixed, G = (softmax - onehot) / n as the loss kernel produces it (every column sums to ~0 over the
+    vertices).  Per entry against fp64, for both split modes: |err| <= 1e-5 * max(|entry|, rms of the result)."""
+    torch = cuda
+    rng = np.random.default_rng(11)
+    K, M, N = 233_000, 128, 64
+    H = rng.standard_normal((K, M)).astype(np.float32)
+    Z = rng.standard_normal((K, N)) * 2
+    P = np.exp(Z - Z.max(1, keepdims=True)); P /= P.sum(1, keepdims=True)
+    P[np.arange(K), rng.integers(0, N, K)] -= 1.0
+    G = (P / K).astype(np.float32)
+    want = H.T.astype(np.float64) @ G.astype(np.float64)
+    rms = float(np.sqrt((want ** 2).mean()))
+    cancel = float((np.abs(H.T).astype(np.float64) @ np.abs(G).astype(np.float64)).mean() / np.abs(want).mean())
+    old = mg.lib().mggcn_tune(b"gemm_split", split)
+    try:
+        got = mg.gemm(torch.from_numpy(H).cuda(), torch.from_numpy(G).cuda(), torch.empty((M, N), device="cuda"),
+                      ta=True).cpu().numpy().astype(np.float64)
+    finally:
+        mg.lib().mggcn_tune(b"gemm_split", old)
+    err = got - want
+    ratio = float((np.abs(err) / np.maximum(np.abs(want), rms)).max())
+    print(f"split={split} cancellation sum|ab|/|sum ab| = {cancel:.0f}x  max err/max(|entry|, rms) = {ratio:.2e}  "
+          f"mean signed err / rms = {err.mean() / rms:+.2e}")
+    assert ratio <= 1e-5, ratio
+
+
 def test_gemm_epilogues_alpha_beta_strided(mg, cuda):
     torch = cuda
     rng = np.random.default_rng(1)
