@@ -25,12 +25,16 @@ class dist_row_dn_matrix {
     // P blocks of N / P rows each: dense blocks assume N % P == 0 (src/dist_matrix.hpp:427-431)
     dist_row_dn_matrix(const dist_context &ctx, std::size_t N, std::size_t M, std::vector<cuda_ptr<r_t>> buffer = {}) {
         if (N % ctx.size() != 0) throw matrix_error("dist_row_dn_matrix: row count is not a multiple of the GPU count");
-        for (std::size_t i = 0; i < ctx.size(); ++i)
+        for (std::size_t i = 0; i < ctx.size(); ++i) {
             As.emplace_back(N / ctx.size(), M, i < buffer.size() ? buffer[i] : nullptr);
+            pin_managed(As[i].buffer(), As[i].size() * sizeof(r_t), (int)i);  // block i lives on GPU i (no-op for device buffers)
+        }
     }
     dist_row_dn_matrix(const std::vector<std::size_t> &p, std::size_t M, std::vector<cuda_ptr<r_t>> buffer = {}) {
-        for (std::size_t i = 0; i + 1 < p.size(); ++i)
+        for (std::size_t i = 0; i + 1 < p.size(); ++i) {
             As.emplace_back(p[i + 1] - p[i], M, i < buffer.size() ? buffer[i] : nullptr);
+            pin_managed(As[i].buffer(), As[i].size() * sizeof(r_t), (int)i);
+        }
     }
     dist_row_dn_matrix(const dist_context &ctx, std::pair<std::size_t, std::size_t> shape)
         : dist_row_dn_matrix(ctx, shape.first, shape.second) {}
@@ -119,7 +123,10 @@ class repl_dn_matrix {
    public:
     repl_dn_matrix() = default;
     repl_dn_matrix(const dist_context &ctx, std::size_t N, std::size_t M) {
-        for (std::size_t i = 0; i < ctx.size(); ++i) As.emplace_back(N, M);
+        for (std::size_t i = 0; i < ctx.size(); ++i) {
+            As.emplace_back(N, M);
+            pin_managed(As[i].buffer(), As[i].size() * sizeof(r_t), (int)i, 'r');  // replica i lives on GPU i
+        }
     }
     repl_dn_matrix(const dist_context &ctx, const matrix_t &A) : repl_dn_matrix(ctx, A.n(), A.m()) {
         ctx.sync();

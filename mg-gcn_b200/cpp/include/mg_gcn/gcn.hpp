@@ -54,7 +54,17 @@ class dist_sparse_linear {
         std::size_t rows = 0;
         for (std::size_t i = 0; i < B.size(); ++i) rows = std::max(rows, B[i].n());
         for (std::size_t i = 0; i < ctx.size(); ++i) p.push_back(p.back() + rows);
-        return {dn_t(p, B.m(), bcast_buffer), dn_t(p, B.m(), bcast_buffer2)};
+        // Staging areas nobody indexes on the host: plain device memory on the GPU that multiplies out of them (the
+        // reference's are managed like everything else, src/gcn.hpp:62-70).  MGGCN_STAGING_MANAGED=1 restores that.
+        static const bool managed = std::getenv("MGGCN_STAGING_MANAGED") != nullptr;
+        std::vector<cuda_ptr<r_t>> buf[2] = {bcast_buffer, bcast_buffer2};  // the caller's, when it passed some
+        for (auto &b : buf)
+            if (b.empty() && !managed && have_device())
+                for (std::size_t i = 0; i < ctx.size(); ++i) {
+                    ctx[i].set();
+                    b.push_back(cuda_malloc<r_t>(rows * B.m()));  // owned by the dn_matrix views built below
+                }
+        return {dn_t(p, B.m(), buf[0]), dn_t(p, B.m(), buf[1])};
     }
 
    public:

@@ -121,4 +121,39 @@ inline void prefetch_to_device(const void *p, std::size_t bytes, int device, cud
     cudaGetLastError();
 }
 
+// Keeps a managed range where it is: preferred location = `device`, and a direct mapping for every other GPU and the
+// host, so that a peer copy, a kernel on another GPU or a host read reaches the pages over NVLink / PCIe instead of
+// migrating them.  The multi-GPU containers (one block or one replica per GPU, read by peers in every exchange stage
+// and every all-reduce) call it for each block; the reference leaves placement to the driver (src/mg_gcn.hpp:74-82).
+// MGGCN_PIN_MANAGED=0 switches it off, =dist / =repl keeps it for one container family only (A/B runs of the
+// layer-stack stress).  `family`: 'd' = dist_row_dn_matrix block, 'r' = repl_dn_matrix replica.
+inline void pin_managed(const void *p, std::size_t bytes, int device, char family = 'd') {
+    static const std::string mode = std::getenv("MGGCN_PIN_MANAGED") ? std::getenv("MGGCN_PIN_MANAGED") : "all";
+    const bool on = mode == "all" || (mode == "dist" && family == 'd') || (mode == "repl" && family == 'r');
+    if (!on || !have_device() || !p || !bytes) return;
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess || a.type != cudaMemoryTypeManaged) {
+        cudaGetLastError();
+        return;
+    }
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) n = 0;
+#if CUDART_VERSION >= 13000
+    auto advise = [&](cudaMemoryAdvise what, int dev) {
+        cudaMemLocation loc{dev == cudaCpuDeviceId ? cudaMemLocationTypeHost : cudaMemLocationTypeDevice, dev == cudaCpuDeviceId ? 0 : dev};
+        cudaMemAdvise(p, bytes, what, loc);
+    };
+#else
+    auto advise = [&](cudaMemoryAdvise what, int dev) { cudaMemAdvise(p, bytes, what, dev); };
+#endif
+    advise(cudaMemAdviseSetPreferredLocation, device);
+    for (int d = 0; d < n; ++d) {
+        int can = d == device;
+        if (!can) cudaDeviceCanAccessPeer(&can, d, device);
+        if (can) advise(cudaMemAdviseSetAccessedBy, d);
+    }
+    advise(cudaMemAdviseSetAccessedBy, cudaCpuDeviceId);
+    cudaGetLastError();
+}
+
 }  // namespace mg_gcn

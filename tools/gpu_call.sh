@@ -20,29 +20,31 @@ bench)
     timeout 900 bash -c "$(declare -f launch); N=$N; launch $*" > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err
     echo "bench rc=$?"; tail -c 3000 gpurun_out/${tag}_bench.json ;;
 stress)
-    runs=${1:-25}
+    # variants: STRESS_VARIANTS="label:ENV=v,ENV=v label2:..." (default: one plain loop); STRESS_BUDGET_S caps the wall time;
+    # STRESS_WARM=1 runs a multi-process bench first.  CUDA_LAUNCH_BLOCKING=1 is NOT a usable variant: one host thread
+    # drives both engines of dist_gcn, and a blocking launch of the first one spins in its peer barrier forever.
+    runs=${1:-20}
     B=mg-gcn_b200/cpp/bin/test_surface
     log=gpurun_out/${tag}_stress.log
+    t0=$(date +%s); budget=${STRESS_BUDGET_S:-100000}
     : > $log
-    nvidia-smi --query-gpu=index,name --format=csv,noheader >> $log
-    if [ "$N" -gt 1 ]; then
+    nvidia-smi --query-gpu=index,name --format=csv,noheader | tr '\n' ';' >> $log; echo >> $log
+    if [ "${STRESS_WARM:-0}" = 1 ] && [ "$N" -gt 1 ]; then
         timeout 300 bash -c "$(declare -f launch); N=$N; launch --steps 5 --warmup 3 --skip-parity --skip-cpu --skip-exposed" > gpurun_out/${tag}_stress_bench.json 2> gpurun_out/${tag}_stress_bench.err
         echo "multi-process job before the loop: rc=$? $(head -c 200 gpurun_out/${tag}_stress_bench.json)" >> $log
     fi
-    loop() {  # $1 = label, rest = env assignments
-        local label=$1; shift; local bad=0
+    for variant in ${STRESS_VARIANTS:-plain:A=1}; do
+        label=${variant%%:*}; envs=$(echo "${variant#*:}" | tr ',' ' ')
+        bad=0; done_=0
         for i in $(seq 1 $runs); do
-            env MGGCN_BARRIER_TIMEOUT_MS=3000 "$@" timeout 120 $B dist > gpurun_out/${tag}_stress_run.txt 2>&1; rc=$?
-            if [ $rc -ne 0 ]; then bad=$((bad + 1)); echo "--- $label run $i rc=$rc" >> $log; grep -v '^$' gpurun_out/${tag}_stress_run.txt | head -n 30 | cut -c1-200 >> $log; fi
+            [ $(( $(date +%s) - t0 )) -ge $budget ] && break
+            env MGGCN_BARRIER_TIMEOUT_MS=3000 $envs timeout 60 $B dist > gpurun_out/${tag}_stress_run.txt 2>&1; rc=$?
+            done_=$((done_ + 1))
+            [ $rc -ne 0 ] && bad=$((bad + 1))
+            echo "--- $label run $i rc=$rc t=$(( $(date +%s) - t0 ))s" >> $log
+            grep -E "first losses|checksum|layer stack|FAILED|mggcn failure" gpurun_out/${tag}_stress_run.txt | cut -c1-160 >> $log
         done
-        echo "$label: $((runs - bad)) of $runs runs green" | tee -a $log
-        return $bad
-    }
-    loop "plain" A=1
-    if [ $? -ne 0 ]; then
-        loop "CUDA_LAUNCH_BLOCKING=1" CUDA_LAUNCH_BLOCKING=1
-        loop "MGGCN_POISON=1" MGGCN_POISON=1
-        loop "two visible devices" CUDA_VISIBLE_DEVICES=0,1
-    fi ;;
+        echo "$label: $((done_ - bad)) of $done_ runs green" | tee -a $log
+    done ;;
 *) echo "usage: $0 suite|bench|stress [tag] [...]"; exit 2 ;;
 esac
