@@ -234,6 +234,33 @@ def cpu_epoch_sample(fwd, bwd, sizes, frac, repeats=1, seconds=15.0, dense_rows=
 # reference binary: timed arm and loss-curve checker
 # ------------------------------------------------------------------------------------------------
 REF_EXE = os.path.join(ROOT, "oracle", "_ref", "mg_gcn_ref")
+# stand-alone dataset writer (generator + file objects linked in, no libmggcn.so): the reference arm generates its
+# files with it, so that nothing of this repository's library is mapped into the process that times the reference
+GEN_EXE = os.path.join(ROOT, "mg-gcn_b200", "cpp", "bin", "mggcn_gen")
+
+
+def maps_libmggcn():
+    """Is this repository's library mapped into the calling process?  (The reference arm reports it: it must not be.)"""
+    try:
+        return any("libmggcn" in line for line in open("/proc/self/maps"))
+    except OSError:
+        return None
+
+
+def write_dataset_standalone(mg, shape, scale, ds):
+    """Runs mggcn_gen for `shape` into directory `ds`; returns {"n", "nnz", "F", "classes"} or None.
+    Same generator code and arguments as mg.generate + mg.write_dataset: the files are byte-identical
+    (tests/test_bench_contract.py)."""
+    if not os.path.exists(GEN_EXE):
+        return None
+    n_raw, edges, f_raw, classes, model, gamma, max_deg = mg.shape_params(shape, scale)
+    cmd = [GEN_EXE, str(n_raw), str(edges), str(f_raw), str(classes), str(model), repr(float(gamma)), str(max_deg), str(SEED),
+           str(int(shape not in mg.UNPERMUTED)), ds]
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=3000)
+        return json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else None
+    except (subprocess.TimeoutExpired, ValueError, IndexError, OSError):
+        return None
 REF_UNSUPPORTED = {
     "papers100M": "the reference cannot run papers100M-shape: 3.23e9 entries exceed its signed 32-bit cuSPARSE indices "
                   "(CUSPARSE_INDEX_32I from x_t = v_t = unsigned, src/main.cpp:43-45, src/mg_gcn.hpp:93-100) and its "
@@ -272,10 +299,15 @@ def run_reference_binary(mg, shape, scale, P, hidden, epochs, dataset=None):
     with tempfile.TemporaryDirectory(prefix="mggcn_ref_") as d:
         ds = os.path.join(d, "permuted", shape)
         t0 = time.time()
-        if dataset is None:
-            dataset = mg.generate(shape, seed=SEED, scale=scale, permute=shape not in mg.UNPERMUTED)
-        A, X, Y, C = dataset
-        mg.write_dataset(ds, A, X, Y)
+        os.makedirs(os.path.dirname(ds), exist_ok=True)
+        meta = write_dataset_standalone(mg, shape, scale, ds) if dataset is None else None
+        standalone = meta is not None
+        if meta is None:
+            if dataset is None:
+                dataset = mg.generate(shape, seed=SEED, scale=scale, permute=shape not in mg.UNPERMUTED)
+            A, X, Y, C = dataset
+            mg.write_dataset(ds, A, X, Y)
+            meta = {"n": A.n, "nnz": A.nnz, "F": int(X.shape[1]), "classes": int(C)}
         os.makedirs(os.path.join(d, "csvs"))
         cmd = [REF_EXE, "-P", str(P), "-R", "1", "-E", str(epochs), "train", ds + "/", str(len(hidden))] + [str(h) for h in hidden]
         t1 = time.time()
@@ -295,7 +327,8 @@ def run_reference_binary(mg, shape, scale, P, hidden, epochs, dataset=None):
         if r.returncode != 0 or len(ep) != epochs:
             return None, {"why": "reference binary failed: " + (r.stderr or r.stdout)[-400:].replace("\n", " | ")}
         info = {"cmd": " ".join(["mg_gcn_ref"] + cmd[1:6] + ["<dataset>"] + cmd[7:]), "wall_s": wall, "dataset_s": t1 - t0,
-                "N": A.n, "nnz": A.nnz, "F": int(X.shape[1]), "classes": int(C)}
+                "N": meta["n"], "nnz": meta["nnz"], "F": meta["F"], "classes": meta["classes"],
+                "dataset_writer": "mggcn_gen (stand-alone executable, no libmggcn.so)" if standalone else "in-process (mg.write_dataset)"}
         try:
             json.dump({"losses": [l for (_, l, _, _) in ep], "acc": [a for (_, _, a, _) in ep], "cmd": info["cmd"]},
                       open(curve_cache_path(shape, scale, P, hidden), "w"))
@@ -352,14 +385,24 @@ def run_reference(args, mg, rank):
     dataset = None
     n_raw, edges, f_raw, classes, *_ = mg.shape_params(args.shape, args.scale)
     small_enough = not (args.shape in REF_UNSUPPORTED and args.scale == 1.0)
-    if small_enough:
+    ep, info = None, {"why": REF_UNSUPPORTED.get(args.shape, "")}
+    if small_enough and os.path.exists(GEN_EXE) and os.path.exists(REF_EXE) and have_gpus(P):
+        # the clean path: dataset from the stand-alone writer, reference binary as a subprocess -- libmggcn.so is never
+        # loaded into this process
+        ep, info = run_reference_binary(mg, args.shape, args.scale, P, hidden, E, None)
+        if ep is not None:
+            N, nnz, F, C = info["N"], info["nnz"], info["F"], info["classes"]
+    if ep is None and small_enough:
         dataset = mg.generate(args.shape, seed=SEED, scale=args.scale, permute=args.shape not in mg.UNPERMUTED)
         A, X, Y, C = dataset
         N, nnz, F = A.n, A.nnz, X.shape[1]
-    else:
+        why_first = info.get("why")
+        ep, info = run_reference_binary(mg, args.shape, args.scale, P, hidden, E, dataset)
+        if ep is None and why_first and "why" in info and not info["why"]:
+            info["why"] = why_first
+    elif ep is None:
         N, nnz, F, C = mg.padded_n(args.shape, args.scale), None, (f_raw + 7) // 8 * 8, classes
     base["config"] = {"workload": workload_text(args.shape, N, nnz, F, hidden, C, args.scale), "P": P}
-    ep, info = run_reference_binary(mg, args.shape, args.scale, P, hidden, E, dataset) if small_enough else (None, {"why": REF_UNSUPPORTED[args.shape]})
     if ep is not None:
         times = [t for (_, _, _, t) in ep[args.warmup:]]
         ms = float(np.mean(times)) * 1e3
@@ -368,7 +411,8 @@ def run_reference(args, mg, rank):
                      "cpu_baseline": {"value": ms, "unit": "ms/epoch", "cores": 1, "kind": "reference",
                                       "sample": "the reference's own CUDA build (cuSPARSE/cuBLAS/NCCL; it has no CPU path), "
                                                 f"all {E} epochs, mean of the last {args.steps}; one host thread drives {P} GPU(s)"},
-                     "reference_detail": {"cmd": info["cmd"], "median_ms": float(np.median(times)) * 1e3,
+                     "reference_detail": {"cmd": info["cmd"], "dataset_writer": info.get("dataset_writer"),
+                                          "libmggcn_mapped_in_this_process": maps_libmggcn(), "median_ms": float(np.median(times)) * 1e3,
                                           "min_ms": float(np.min(times)) * 1e3, "losses": [l for (_, l, _, _) in ep][:12],
                                           "wall_s": info["wall_s"]}})
         emit(base)

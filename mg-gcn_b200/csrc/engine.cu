@@ -1088,6 +1088,11 @@ static int validate_csr(int64_t rows, int64_t cols, const uint64_t *rp, const ui
 // with X = 500 GB/s (what a rank receives while every rank pulls and multiplies) and R = the gather rate the SpMM
 // sustains (16 TB/s out of the L2, 6.5 TB/s when a block of B is larger than half the L2), i.e. the exchange is
 // the longer side when the entries per row and block are fewer than R / X.
+// Scope of the rule: X and R are B200 / NVLink-5 figures measured in this repository (DESIGN.md section 4 and
+// profiles/l2_peak.json); on another part set the grouping with mggcn_tune("xgroups", 1 | 2) instead.  The decision is
+// taken per rank from that rank's own block row, without an exchange: ranks whose rows sit near the threshold may
+// group differently, which changes their launch counts but not the protocol -- every rank passes the same number of
+// stage barriers and publishes the same flags whatever its grouping (tests/dist_engine_check.py runs mixed groupings).
 static void choose_groups(mggcn_engine *e, const uint64_t *const *blk_rowptr) {
     if (!e->grouped || e->groups_chosen) return;
     e->groups_chosen = true;

@@ -60,3 +60,27 @@ def test_own_arm_refuses_to_run_without_a_gpu():
     assert r.returncode != 0
     assert "needs a GPU" in r.stderr
     assert not [l for l in r.stdout.splitlines() if l.strip().startswith("{")]
+
+
+def test_standalone_dataset_writer_matches_the_library(mg, tmp_path):
+    """bench.py's reference arm writes its dataset with mg-gcn_b200/cpp/bin/mggcn_gen (no libmggcn.so in that
+    process); the files must be the ones the repo arm's in-process generator writes, byte for byte."""
+    import subprocess
+    exe = os.path.join(ROOT, "mg-gcn_b200", "cpp", "bin", "mggcn_gen")
+    if not os.path.exists(exe):
+        r = subprocess.run(["make", "-C", os.path.join(ROOT, "mg-gcn_b200", "cpp"), "-j4"], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-2000:]
+    ldd = subprocess.run(["ldd", exe], capture_output=True, text=True).stdout
+    assert "libmggcn" not in ldd and "libcudart" not in ldd
+    for shape, permute in (((3000, 40000, 50, 7, 0, 0.0, 0), 1), ((2500, 60000, 33, 41, 1, 2.2, 300), 0)):
+        n_raw, edges, f_raw, classes, model, gamma, max_deg = shape
+        a, b = str(tmp_path / f"exe{permute}"), str(tmp_path / f"lib{permute}")
+        r = subprocess.run([exe, str(n_raw), str(edges), str(f_raw), str(classes), str(model), repr(gamma), str(max_deg), "1",
+                            str(permute), a], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        meta = json.loads(r.stdout.strip().splitlines()[-1])
+        A, X, Y, C = mg.generate(shape, seed=1, permute=bool(permute))
+        mg.write_dataset(b, A, X, Y)
+        assert meta == {"n": A.n, "nnz": A.nnz, "F": X.shape[1], "classes": C}
+        for f in ("graph.bin", "features.bin", "labels.bin", "sets.bin"):
+            assert open(os.path.join(a, f), "rb").read() == open(os.path.join(b, f), "rb").read(), f
